@@ -1,0 +1,295 @@
+// C ABI of libfa_b200.so (see include/fa_b200.h).  Host-side launcher: argument validation, device
+// check, workspace carving, kernel dispatch.  B200 equivalent of mha_fwd / set_params_fprop / run_fmha_fprop
+// (csrc/flash_attn/fmha_api.cpp:38-242, src/fmha_fprop_kernel_dispatch.cu:90-134) -- but torch-free, never
+// allocating, never synchronising, and reporting errors by return code instead of exit(1)
+// (src/fmha_utils.h:37-48).
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "fa_common.cuh"
+#include "fa_kernels.h"
+
+namespace fa {
+
+namespace {
+
+thread_local char g_last_error[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_last_error, sizeof(g_last_error), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+  return fail(FA_ERR_CUDA, "%s: %s (%s)", what, cudaGetErrorName(e), cudaGetErrorString(e));
+}
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+inline uint64_t round_up(uint64_t x, uint64_t m) { return (x + m - 1) / m * m; }
+
+int check_device() {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+  static int cached_major[64];
+  static bool cached[64];
+  int major = 0;
+  if (dev < 64 && cached[dev]) {
+    major = cached_major[dev];
+  } else {
+    e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaDeviceGetAttribute");
+    if (dev < 64) { cached_major[dev] = major; cached[dev] = true; }
+  }
+  if (major != 10)
+    return fail(FA_ERR_UNSUPPORTED_DEVICE, "libfa_b200 needs a compute capability 10.x (sm_100a) device, found %d.x", major);
+  return FA_OK;
+}
+
+// Shape / dtype / stride checks corresponding to the TORCH_CHECKs of fmha_api.cpp:127-170.
+int validate_common(const fa_params* p, bool bwd, bool block) {
+  if (p == nullptr) return fail(FA_ERR_INVALID_ARGUMENT, "params is NULL");
+  if (p->b <= 0) return fail(FA_ERR_INVALID_ARGUMENT, "batch size must be positive (got %d)", p->b);
+  if (p->h <= 0) return fail(FA_ERR_INVALID_ARGUMENT, "number of heads must be positive (got %d)", p->h);
+  if (p->d <= 0 || p->d % 8 != 0 || p->d > 128)
+    return fail(FA_ERR_INVALID_ARGUMENT, "head dim must be a multiple of 8 and <= 128 (got %d)", p->d);
+  if (p->total_q < 0 || p->total_k < 0) return fail(FA_ERR_INVALID_ARGUMENT, "negative token count");
+  if (p->max_seqlen_q < 0 || p->max_seqlen_k < 0) return fail(FA_ERR_INVALID_ARGUMENT, "negative max_seqlen");
+  if (!(p->p_dropout >= 0.f && p->p_dropout < 1.f))
+    return fail(FA_ERR_INVALID_ARGUMENT, "p_dropout must be in [0, 1) (got %f)", (double)p->p_dropout);
+  if (p->is_bf16 != 0 && p->is_bf16 != 1) return fail(FA_ERR_INVALID_ARGUMENT, "is_bf16 must be 0 or 1");
+  if (p->impl < FA_IMPL_AUTO || p->impl > FA_IMPL_SIMT) return fail(FA_ERR_INVALID_ARGUMENT, "unknown impl %d", p->impl);
+  if (p->cu_seqlens_q == nullptr || p->cu_seqlens_k == nullptr)
+    return fail(FA_ERR_INVALID_ARGUMENT, "cu_seqlens_q / cu_seqlens_k must be non-NULL int32 device arrays");
+  if (p->seqlen_q_rounded < p->max_seqlen_q)
+    return fail(FA_ERR_INVALID_ARGUMENT, "seqlen_q_rounded (%d) < max_seqlen_q (%d)", p->seqlen_q_rounded, p->max_seqlen_q);
+  if (p->softmax_lse == nullptr) return fail(FA_ERR_INVALID_ARGUMENT, "softmax_lse is NULL");
+  if (p->s_dmask != nullptr && p->seqlen_k_rounded < p->max_seqlen_k)
+    return fail(FA_ERR_INVALID_ARGUMENT, "seqlen_k_rounded (%d) < max_seqlen_k (%d)", p->seqlen_k_rounded, p->max_seqlen_k);
+
+  struct T { const void* ptr; int64_t rs, hs; const char* name; bool need; };
+  const T ts[] = {
+      {p->q, p->q_row_stride, p->q_head_stride, "q", true},
+      {p->k, p->k_row_stride, p->k_head_stride, "k", true},
+      {p->v, p->v_row_stride, p->v_head_stride, "v", true},
+      {p->o, p->o_row_stride, p->o_head_stride, "o", true},
+      {p->dout, p->do_row_stride, p->do_head_stride, "dout", bwd},
+      {p->dq, p->dq_row_stride, p->dq_head_stride, "dq", bwd},
+      {p->dk, p->dk_row_stride, p->dk_head_stride, "dk", bwd},
+      {p->dv, p->dv_row_stride, p->dv_head_stride, "dv", bwd},
+  };
+  for (const T& t : ts) {
+    if (!t.need) continue;
+    const bool is_k_side = (t.name[0] == 'k' || t.name[0] == 'v' || (t.name[0] == 'd' && (t.name[1] == 'k' || t.name[1] == 'v')));
+    const int total = is_k_side ? p->total_k : p->total_q;
+    if (t.ptr == nullptr && total > 0) return fail(FA_ERR_INVALID_ARGUMENT, "%s is NULL", t.name);
+    if (!aligned16(t.ptr)) return fail(FA_ERR_INVALID_ARGUMENT, "%s must be 16-byte aligned", t.name);
+    if (t.rs % 8 != 0 || t.hs % 8 != 0 || t.rs < p->d || t.hs < p->d)
+      return fail(FA_ERR_INVALID_ARGUMENT, "%s strides (row %lld, head %lld) must be multiples of 8 elements and >= d",
+                  t.name, (long long)t.rs, (long long)t.hs);
+  }
+  if (bwd && p->softmax_d == nullptr) return fail(FA_ERR_INVALID_ARGUMENT, "softmax_d is NULL");
+  if (block) {
+    if (p->blockmask == nullptr) return fail(FA_ERR_INVALID_ARGUMENT, "blockmask is NULL");
+    if (p->blockmask_nrow <= 0 || p->blockmask_ncol <= 0)
+      return fail(FA_ERR_INVALID_ARGUMENT, "blockmask shape must be positive (got %d x %d)", p->blockmask_nrow, p->blockmask_ncol);
+    if (p->is_causal) return fail(FA_ERR_INVALID_ARGUMENT, "blocksparse attention does not support causal (flash_blocksparse_attn_interface.py:21)");
+  } else if (p->blockmask != nullptr) {
+    return fail(FA_ERR_INVALID_ARGUMENT, "blockmask given to a dense entry point");
+  }
+  return FA_OK;
+}
+
+__global__ void expand_blockmask_kernel(const int32_t* __restrict__ conv, int nrow, int ncol, uint8_t* __restrict__ dense) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;   // over (ncol, nrow)
+  if (idx >= nrow * ncol) return;
+  const int c = idx / nrow;
+  const int val = conv[idx];
+  if (val >= 0) {
+    const int r = val >> 2;
+    if (r < nrow) dense[r * ncol + c] = 1;
+  }
+}
+
+template <typename V>
+__global__ void gather_rows_kernel(V* __restrict__ dst, const V* __restrict__ src, const int64_t* __restrict__ idx,
+                                   int64_t n, int64_t row_vecs) {
+  // one CTA row-group per blockIdx.y-strided index; threads stride over the row's vectors
+  for (int64_t i = blockIdx.x; i < n; i += gridDim.x) {
+    const V* s = src + idx[i] * row_vecs;
+    V* d = dst + i * row_vecs;
+    for (int64_t c = threadIdx.x; c < row_vecs; c += blockDim.x) d[c] = __ldg(s + c);
+  }
+}
+template <typename V>
+__global__ void scatter_rows_kernel(V* __restrict__ dst, const V* __restrict__ src, const int64_t* __restrict__ idx,
+                                    int64_t n, int64_t row_vecs) {
+  for (int64_t i = blockIdx.x; i < n; i += gridDim.x) {
+    const V* s = src + i * row_vecs;
+    V* d = dst + idx[i] * row_vecs;
+    for (int64_t c = threadIdx.x; c < row_vecs; c += blockDim.x) d[c] = __ldg(s + c);
+  }
+}
+
+template <bool kGather>
+int move_rows(void* dst, const void* src, const int64_t* indices, int64_t n, int64_t row_bytes, void* stream) {
+  if (n < 0 || row_bytes < 0) return fail(FA_ERR_INVALID_ARGUMENT, "negative size");
+  if (n == 0 || row_bytes == 0) return FA_OK;
+  if (dst == nullptr || src == nullptr || indices == nullptr) return fail(FA_ERR_INVALID_ARGUMENT, "NULL pointer");
+  if (row_bytes % 4 != 0) return fail(FA_ERR_INVALID_ARGUMENT, "row_bytes must be a multiple of 4 (got %lld)", (long long)row_bytes);
+  int rc = check_device();
+  if (rc != FA_OK) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool v16 = row_bytes % 16 == 0 && aligned16(dst) && aligned16(src);
+  const int64_t vecs = v16 ? row_bytes / 16 : row_bytes / 4;
+  int threads = 32;
+  while (threads < 256 && threads < vecs) threads *= 2;
+  const unsigned grid = static_cast<unsigned>(n < 148 * 16 ? n : 148 * 16);
+  if (v16) {
+    if (kGather) gather_rows_kernel<uint4><<<grid, threads, 0, st>>>((uint4*)dst, (const uint4*)src, indices, n, vecs);
+    else scatter_rows_kernel<uint4><<<grid, threads, 0, st>>>((uint4*)dst, (const uint4*)src, indices, n, vecs);
+  } else {
+    if (kGather) gather_rows_kernel<uint32_t><<<grid, threads, 0, st>>>((uint32_t*)dst, (const uint32_t*)src, indices, n, vecs);
+    else scatter_rows_kernel<uint32_t><<<grid, threads, 0, st>>>((uint32_t*)dst, (const uint32_t*)src, indices, n, vecs);
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(e, kGather ? "gather_rows launch" : "scatter_rows launch");
+  return FA_OK;
+}
+
+uint64_t blockmask_bytes(const fa_params* p) {
+  return round_up(static_cast<uint64_t>(p->blockmask_nrow) * p->blockmask_ncol, 256);
+}
+
+// Builds the dense byte mask in the head of the workspace.
+int prepare_blockmask(const fa_params* p, cudaStream_t st, BlockMaskView* bm) {
+  const uint64_t need = blockmask_bytes(p);
+  if (p->workspace == nullptr || p->workspace_bytes < need)
+    return fail(FA_ERR_WORKSPACE, "workspace too small: need %llu bytes, have %llu", (unsigned long long)need,
+                (unsigned long long)p->workspace_bytes);
+  uint8_t* dense = static_cast<uint8_t*>(p->workspace);
+  cudaError_t e = cudaMemsetAsync(dense, 0, need, st);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(blockmask)");
+  e = launch_expand_blockmask(p->blockmask, p->blockmask_nrow, p->blockmask_ncol, dense, st);
+  if (e != cudaSuccess) return cuda_fail(e, "expand_blockmask launch");
+  bm->dense = dense;
+  bm->nrow = p->blockmask_nrow;
+  bm->ncol = p->blockmask_ncol;
+  return FA_OK;
+}
+
+int run_fwd(const fa_params* p, void* stream, bool block) {
+  g_last_error[0] = 0;
+  int rc = validate_common(p, /*bwd=*/false, block);
+  if (rc != FA_OK) return rc;
+  rc = check_device();
+  if (rc != FA_OK) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  BlockMaskView bm{nullptr, 0, 0};
+  if (block) {
+    rc = prepare_blockmask(p, st, &bm);
+    if (rc != FA_OK) return rc;
+  }
+  if (p->impl == FA_IMPL_SIMT) {
+    cudaError_t e = launch_simt_fwd(*p, bm, /*only_sdmask=*/false, st);
+    if (e != cudaSuccess) return cuda_fail(e, "simt forward launch");
+    return FA_OK;
+  }
+  const char* msg = nullptr;
+  cudaError_t e = launch_fwd_sm100(*p, bm, st, &msg);
+  if (e != cudaSuccess) return msg ? fail(FA_ERR_INVALID_ARGUMENT, "%s", msg) : cuda_fail(e, "tcgen05 forward launch");
+  if (p->s_dmask != nullptr) {
+    // debug output: +-P from the final lse and the position-keyed dropout stream
+    e = launch_simt_fwd(*p, bm, /*only_sdmask=*/true, st);
+    if (e != cudaSuccess) return cuda_fail(e, "S_dmask kernel launch");
+  }
+  return FA_OK;
+}
+
+int run_bwd(const fa_params* p, void* stream, bool block) {
+  g_last_error[0] = 0;
+  int rc = validate_common(p, /*bwd=*/true, block);
+  if (rc != FA_OK) return rc;
+  rc = check_device();
+  if (rc != FA_OK) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  BlockMaskView bm{nullptr, 0, 0};
+  if (block) {
+    rc = prepare_blockmask(p, st, &bm);
+    if (rc != FA_OK) return rc;
+  }
+  if (p->impl == FA_IMPL_SIMT) {
+    cudaError_t e = launch_simt_bwd(*p, bm, st);
+    if (e != cudaSuccess) return cuda_fail(e, "simt backward launch");
+    return FA_OK;
+  }
+  const uint64_t need = fa_workspace_bytes(p, block ? FA_OP_BWD_BLOCK : FA_OP_BWD);
+  if (need > 0 && (p->workspace == nullptr || p->workspace_bytes < need))
+    return fail(FA_ERR_WORKSPACE, "workspace too small: need %llu bytes, have %llu", (unsigned long long)need,
+                (unsigned long long)p->workspace_bytes);
+  const char* msg = nullptr;
+  cudaError_t e = launch_bwd_sm100(*p, bm, st, &msg);
+  if (e != cudaSuccess) return msg ? fail(FA_ERR_INVALID_ARGUMENT, "%s", msg) : cuda_fail(e, "tcgen05 backward launch");
+  return FA_OK;
+}
+
+}  // namespace
+
+cudaError_t launch_expand_blockmask(const int32_t* converted, int nrow, int ncol, uint8_t* dense, cudaStream_t stream) {
+  const int n = nrow * ncol;
+  expand_blockmask_kernel<<<(n + 255) / 256, 256, 0, stream>>>(converted, nrow, ncol, dense);
+  return cudaGetLastError();
+}
+
+}  // namespace fa
+
+// ------------------------------------------------------------------------------------------------
+// exported C ABI
+// ------------------------------------------------------------------------------------------------
+extern "C" {
+#pragma GCC visibility push(default)
+
+int fa_abi_version(void) { return FA_B200_ABI_VERSION; }
+uint64_t fa_sizeof_params(void) { return sizeof(fa_params); }
+const char* fa_last_error(void) { return fa::g_last_error; }
+
+uint64_t fa_workspace_bytes(const fa_params* p, int op) {
+  if (p == nullptr) return 0;
+  uint64_t bytes = 0;
+  if (op == FA_OP_FWD_BLOCK || op == FA_OP_BWD_BLOCK) bytes += fa::blockmask_bytes(p);
+  if ((op == FA_OP_BWD || op == FA_OP_BWD_BLOCK) && p->impl != FA_IMPL_SIMT) bytes += fa::bwd_sm100_workspace_bytes(*p);
+  return bytes;
+}
+
+// The dropout stream is keyed by position, so one call consumes one "slot" of the generator; the increment is
+// kept a multiple of 4 like ATen's philox_cuda_state (fmha_api.cpp:228-234).
+uint64_t fa_philox_increment(const fa_params* p) { return (p != nullptr && p->p_dropout > 0.f) ? 4 : 0; }
+
+int fa_fwd(const fa_params* p, void* stream) { return fa::run_fwd(p, stream, false); }
+int fa_bwd(const fa_params* p, void* stream) { return fa::run_bwd(p, stream, false); }
+int fa_fwd_block(const fa_params* p, void* stream) { return fa::run_fwd(p, stream, true); }
+int fa_bwd_block(const fa_params* p, void* stream) { return fa::run_bwd(p, stream, true); }
+
+int fa_gather_rows(void* dst, const void* src, const int64_t* indices, int64_t n_indices, int64_t row_bytes, void* stream) {
+  fa::g_last_error[0] = 0;
+  return fa::move_rows<true>(dst, src, indices, n_indices, row_bytes, stream);
+}
+int fa_scatter_rows(void* dst, const void* src, const int64_t* indices, int64_t n_indices, int64_t row_bytes, void* stream) {
+  fa::g_last_error[0] = 0;
+  return fa::move_rows<false>(dst, src, indices, n_indices, row_bytes, stream);
+}
+
+void fa_dropout_keep8_host(uint64_t seed, uint64_t offset, uint32_t bh, uint32_t qrow, uint32_t kgroup, float p_dropout,
+                           uint8_t* keep) {
+  const fa::PhiloxKey pk = fa::make_philox_key(seed, offset);
+  const uint4 r = fa::dropout_rand8(pk, bh, qrow, kgroup);
+  const uint32_t thr = fa::keep_threshold_u16(p_dropout);
+  for (int e = 0; e < 8; ++e) keep[e] = fa::rand8_get(r, e) <= thr ? 1 : 0;
+}
+
+#pragma GCC visibility pop
+}  // extern "C"

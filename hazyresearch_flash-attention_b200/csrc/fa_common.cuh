@@ -1,0 +1,116 @@
+// Shared host/device definitions for the attention kernels: the kernel argument block, per-sequence
+// bounds, the position-keyed Philox dropout stream and small numeric helpers.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/fa_b200.h"
+
+namespace fa {
+
+#define FA_HD __host__ __device__ __forceinline__
+
+// ------------------------------------------------------------------------------------------------
+// Philox4x32, 7 rounds (same round count as the reference RNG, csrc/flash_attn/src/philox.cuh:30-59).
+// The counter is keyed by POSITION, not by thread layout:
+//     counter = (query row in sequence, key index / 8, batch * h + head, offset low 32 bits)
+//     key     = (seed low 32 bits, seed high 32 bits ^ offset high 32 bits)
+// One call yields 8 x 16-bit uniforms for 8 consecutive keys; a position is kept iff
+// u16 <= floor((1 - p) * 65535)  (16-bit compare as in src/fmha/softmax.h:268-279, fmha_api.cpp:104).
+// Forward, backward and the S_dmask debug kernel therefore agree for any tiling.
+// ------------------------------------------------------------------------------------------------
+struct PhiloxKey {
+  uint32_t k0, k1, c3;
+};
+
+FA_HD PhiloxKey make_philox_key(uint64_t seed, uint64_t offset) {
+  PhiloxKey k;
+  k.k0 = static_cast<uint32_t>(seed);
+  k.k1 = static_cast<uint32_t>(seed >> 32) ^ static_cast<uint32_t>(offset >> 32);
+  k.c3 = static_cast<uint32_t>(offset);
+  return k;
+}
+
+FA_HD uint32_t mulhi32(uint32_t a, uint32_t b) {
+#ifdef __CUDA_ARCH__
+  return __umulhi(a, b);
+#else
+  return static_cast<uint32_t>((static_cast<uint64_t>(a) * b) >> 32);
+#endif
+}
+
+FA_HD uint4 philox4x32_7(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int r = 0; r < 7; ++r) {
+    const uint32_t hi0 = mulhi32(M0, c0), lo0 = M0 * c0;
+    const uint32_t hi1 = mulhi32(M1, c2), lo1 = M1 * c2;
+    const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+    c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+    k0 += W0; k1 += W1;
+  }
+  return make_uint4(c0, c1, c2, c3);
+}
+
+// 8 uniforms (16 bit each) for keys 8*kgroup .. 8*kgroup+7 of query row qrow.
+FA_HD uint4 dropout_rand8(const PhiloxKey& key, uint32_t bh, uint32_t qrow, uint32_t kgroup) {
+  return philox4x32_7(qrow, kgroup, bh, key.c3, key.k0, key.k1);
+}
+FA_HD uint32_t rand8_get(const uint4& r, int e) {   // e in [0, 8)
+  const uint32_t w = (e >> 1) == 0 ? r.x : (e >> 1) == 1 ? r.y : (e >> 1) == 2 ? r.z : r.w;
+  return (e & 1) ? (w >> 16) : (w & 0xFFFFu);
+}
+FA_HD uint32_t keep_threshold_u16(float p_dropout) {
+  const float keep = 1.f - p_dropout;
+  return static_cast<uint32_t>(floorf(keep * 65535.0f));
+}
+
+// ------------------------------------------------------------------------------------------------
+// Per-sequence bounds (restates BlockInfoPadded, csrc/flash_attn/src/fmha_kernel.h:45-76).
+// ------------------------------------------------------------------------------------------------
+struct SeqInfo {
+  int q_begin, k_begin, seqlen_q, seqlen_k;
+  __device__ __forceinline__ SeqInfo(const int32_t* cu_q, const int32_t* cu_k, int b) {
+    q_begin = cu_q[b];
+    k_begin = cu_k[b];
+    seqlen_q = cu_q[b + 1] - q_begin;
+    seqlen_k = cu_k[b + 1] - k_begin;
+  }
+};
+
+template <bool kBf16>
+struct Elem;
+template <>
+struct Elem<true> {
+  using T = __nv_bfloat16;
+  static __device__ __forceinline__ float to_float(T x) { return __bfloat162float(x); }
+  static __device__ __forceinline__ T from_float(float x) { return __float2bfloat16_rn(x); }
+};
+template <>
+struct Elem<false> {
+  using T = __half;
+  static __device__ __forceinline__ float to_float(T x) { return __half2float(x); }
+  static __device__ __forceinline__ T from_float(float x) { return __float2half_rn(x); }
+};
+
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+
+// Blocksparse helper: the converted mask (ncol, nrow) lists, for each 256-wide key block column, the
+// 16-row query blocks that attend to it (x4, low bits = first/last flags), padded with -1
+// (flash_attn/flash_blocksparse_attn_interface.py:8-40).  The kernels work from the equivalent dense
+// (nrow, ncol) 0/1 byte mask, rebuilt on device by expand_blockmask_kernel.
+struct BlockMaskView {
+  const uint8_t* dense;   // (nrow, ncol) or nullptr
+  int nrow, ncol;
+  __device__ __forceinline__ bool on(int qrow, int kcol) const {
+    if (dense == nullptr) return true;
+    const int r = qrow >> 4, c = kcol >> 8;
+    if (r >= nrow || c >= ncol) return false;
+    return dense[r * ncol + c] != 0;
+  }
+};
+
+}  // namespace fa

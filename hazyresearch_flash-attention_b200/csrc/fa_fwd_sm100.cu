@@ -1,0 +1,516 @@
+// FlashAttention forward for sm_100a: TMA -> shared-memory ring -> tcgen05.mma with TMEM accumulators,
+// warp-specialised (2 softmax warpgroups ping-ponging two 128-row Q tiles, 1 TMA producer warp,
+// 1 MMA issuer warp).  Replaces fmha_fprop_loop_kernel / device_1xN_loop of the reference
+// (csrc/flash_attn/src/fmha_fprop_kernel_dispatch.cu:32-35, src/fmha_fprop_kernel_1xN.h:226-717) with the
+// loop order inverted: a CTA owns 256 query rows and streams K/V blocks, so O and the softmax statistics
+// never leave the SM (the reference round-trips an fp32 O partial through global memory per K block).
+//
+// Per CTA:  S_t = Q_t K_j^T  (SS MMA, 128x128xDPAD)  ->  softmax warpgroup t: online softmax in registers,
+//           P_t written back to TMEM as 16-bit (aliasing S_t)  ->  O_t += P_t V_j (TS MMA, 128xDPADx128).
+// TMEM columns: S0 [0,128) | S1 [128,256) | O0 [256,256+DPAD) | O1 [384,384+DPAD).
+#include <cudaTypedefs.h>
+
+#include "fa_common.cuh"
+#include "fa_kernels.h"
+#include "sm100_ptx.cuh"
+
+namespace fa {
+
+namespace {
+
+constexpr int kBlockM = 128;      // rows per Q tile (= UMMA M)
+constexpr int kTilesPerCta = 2;   // Q tiles per CTA (ping-pong)
+constexpr int kBlockN = 128;      // keys per K/V block
+constexpr int kNumThreads = 384;  // warps 0-3: softmax tile 0, 4-7: softmax tile 1, 8: TMA, 9: MMA, 10-11: idle
+constexpr int kSoftmaxRegs = 216;
+constexpr int kOtherRegs = 72;
+constexpr float kRescaleThreshold = 8.0f;   // lazy rescale: only when the row max grows by > 2^8
+
+template <int DPAD>
+struct FwdSmem {
+  static constexpr int kStages = DPAD == 128 ? 2 : 4;
+  static constexpr int kTileBytes = kBlockM * DPAD * 2;          // one [128 x DPAD] 16-bit tile
+  static constexpr int kSubTileBytes = kBlockM * 128;            // [128 rows x 64 cols] swizzle-128B sub tile
+  static constexpr int kQOff = 0;
+  static constexpr int kKOff = kQOff + kTilesPerCta * kTileBytes;
+  static constexpr int kVOff = kKOff + kStages * kTileBytes;
+  static constexpr int kBarOff = kVOff + kStages * kTileBytes;
+  // barriers: q_full[2], s_full[2], p_full[2], o_full[2], k_full[S], k_empty[S], v_full[S], v_empty[S]
+  static constexpr int kNumBars = 8 + 4 * kStages;
+  static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
+  static constexpr int kListOff = kTmemPtrOff + 16;              // blocksparse: active KV block list (int16)
+  static constexpr int kMaxListEntries = 1024;
+  static constexpr int kTotal = kListOff + kMaxListEntries * 2;
+  static constexpr int kDynamicBytes = kTotal + 1024;            // + alignment slack
+};
+
+struct FwdTensorMaps {
+  CUtensorMap q, k, v;
+};
+
+template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse>
+__global__ void __launch_bounds__(kNumThreads, 1)
+fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, const BlockMaskView bm) {
+  using L = FwdSmem<DPAD>;
+  constexpr int ST = L::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int bidb = blockIdx.z, bidh = blockIdx.y;
+  const SeqInfo seq(p.cu_seqlens_q, p.cu_seqlens_k, bidb);
+  // heaviest (latest) causal tiles first
+  const int m_block = kCausal ? (gridDim.x - 1 - blockIdx.x) : blockIdx.x;
+  const int q0 = m_block * (kBlockM * kTilesPerCta);
+  if (q0 >= seq.seqlen_q) return;   // CTA-uniform
+
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
+  uint64_t* q_full = bars + 0;
+  uint64_t* s_full = bars + 2;
+  uint64_t* p_full = bars + 4;
+  uint64_t* o_full = bars + 6;
+  uint64_t* k_full = bars + 8;
+  uint64_t* k_empty = k_full + ST;
+  uint64_t* v_full = k_empty + ST;
+  uint64_t* v_empty = v_full + ST;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + L::kTmemPtrOff);
+  int16_t* blk_list = reinterpret_cast<int16_t*>(smem + L::kListOff);
+  __shared__ int s_num_active;
+
+  // number of KV blocks this CTA walks, and how many of them each Q tile takes part in (a prefix)
+  const int nkv_total = (seq.seqlen_k + kBlockN - 1) / kBlockN;
+  int nu = nkv_total;
+  int cnt[kTilesPerCta];
+#pragma unroll
+  for (int t = 0; t < kTilesPerCta; ++t) {
+    const int r0 = q0 + t * kBlockM;
+    int c = (r0 < seq.seqlen_q) ? nkv_total : 0;
+    if (kCausal && c > 0) c = min(c, r0 / kBlockN + 1);
+    cnt[t] = c;
+  }
+  if (kCausal) nu = max(cnt[0], cnt[1]);
+
+  if (kSparse) {
+    // Active KV blocks = those with at least one nonzero (16 x 256) mask block among this CTA's rows.
+    // flags are written into blk_list[512 + j] first, then compacted in order by warp 0.
+    const int r_lo = q0 >> 4;
+    const int r_hi = min((min(q0 + kBlockM * kTilesPerCta, seq.seqlen_q) + 15) >> 4, bm.nrow);
+    for (int j = threadIdx.x; j < nkv_total; j += kNumThreads) {
+      const int c = (j * kBlockN) >> 8;
+      bool any = false;
+      if (c < bm.ncol)
+        for (int r = r_lo; r < r_hi; ++r) any |= bm.dense[r * bm.ncol + c] != 0;
+      blk_list[512 + j] = any ? 1 : 0;
+    }
+    __syncthreads();
+    if (warp == 0) {
+      int n_act = 0;
+      for (int j0 = 0; j0 < nkv_total; j0 += 32) {
+        const int j = j0 + lane;
+        const bool f = j < nkv_total && blk_list[512 + j] != 0;
+        const uint32_t ball = __ballot_sync(0xffffffffu, f);
+        if (f) blk_list[n_act + __popc(ball & ((1u << lane) - 1))] = static_cast<int16_t>(j);
+        n_act += __popc(ball);
+      }
+      if (lane == 0) s_num_active = n_act;
+    }
+    __syncthreads();
+    nu = s_num_active;
+#pragma unroll
+    for (int t = 0; t < kTilesPerCta; ++t) cnt[t] = cnt[t] > 0 ? nu : 0;
+  }
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int t = 0; t < 2; ++t) {
+      mbar_init(&q_full[t], 1);
+      mbar_init(&s_full[t], 1);
+      mbar_init(&p_full[t], kBlockM);
+      mbar_init(&o_full[t], 1);
+    }
+    for (int s = 0; s < ST; ++s) {
+      mbar_init(&k_full[s], 1);
+      mbar_init(&k_empty[s], 1);
+      mbar_init(&v_full[s], 1);
+      mbar_init(&v_empty[s], 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(tmem_ptr_smem, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  uint8_t* sQ = smem + L::kQOff;
+  uint8_t* sK = smem + L::kKOff;
+  uint8_t* sV = smem + L::kVOff;
+
+  if (warp >= 8) {
+    setmaxnreg_dec<kOtherRegs>();
+    if (warp == 8) {
+      // ===================================== TMA producer =====================================
+      if (elect_one()) {
+        tma_prefetch_desc(&maps.q);
+        tma_prefetch_desc(&maps.k);
+        tma_prefetch_desc(&maps.v);
+#pragma unroll
+        for (int t = 0; t < kTilesPerCta; ++t) {
+          if (cnt[t] > 0) {
+            mbar_arrive_expect_tx(&q_full[t], L::kTileBytes);
+#pragma unroll
+            for (int c = 0; c < DPAD / 64; ++c)
+              tma_load_3d(sQ + t * L::kTileBytes + c * L::kSubTileBytes, &maps.q, &q_full[t], c * 64, bidh,
+                          seq.q_begin + q0 + t * kBlockM);
+          }
+        }
+        for (int u = 0; u < nu; ++u) {
+          const int j = kSparse ? blk_list[u] : u;
+          const int s = u % ST;
+          const uint32_t ph = (u / ST) & 1;
+          mbar_wait(&k_empty[s], ph ^ 1);
+          mbar_arrive_expect_tx(&k_full[s], L::kTileBytes);
+#pragma unroll
+          for (int c = 0; c < DPAD / 64; ++c)
+            tma_load_3d(sK + s * L::kTileBytes + c * L::kSubTileBytes, &maps.k, &k_full[s], c * 64, bidh,
+                        seq.k_begin + j * kBlockN);
+          mbar_wait(&v_empty[s], ph ^ 1);
+          mbar_arrive_expect_tx(&v_full[s], L::kTileBytes);
+#pragma unroll
+          for (int c = 0; c < DPAD / 64; ++c)
+            tma_load_3d(sV + s * L::kTileBytes + c * L::kSubTileBytes, &maps.v, &v_full[s], c * 64, bidh,
+                        seq.k_begin + j * kBlockN);
+        }
+      }
+    } else if (warp == 9) {
+      // ===================================== MMA issuer =======================================
+      if (elect_one()) {
+        const uint32_t idesc_qk = make_idesc_f16(kBf16, kBlockM, kBlockN, false, false);
+        const uint32_t idesc_pv = make_idesc_f16(kBf16, kBlockM, DPAD, false, true);
+        const uint32_t sQ_addr = smem_u32(sQ), sK_addr = smem_u32(sK), sV_addr = smem_u32(sV);
+
+        // S_t = Q_t K^T : A = Q tile (K-major), B = K tile (K-major); DPAD/16 MMAs of K=16
+        auto issue_qk = [&](int t, int stage) {
+          const uint32_t a0 = sQ_addr + t * L::kTileBytes, b0 = sK_addr + stage * L::kTileBytes;
+#pragma unroll
+          for (int kk = 0; kk < DPAD / 16; ++kk) {
+            const uint32_t off = (kk >> 2) * L::kSubTileBytes + (kk & 3) * 32;
+            umma_ss(tmem_base + t * 128, make_smem_desc_sw128(a0 + off, 16, 1024),
+                    make_smem_desc_sw128(b0 + off, 16, 1024), idesc_qk, kk > 0 ? 1u : 0u);
+          }
+        };
+        // O_t += P_t V : A = P_t in TMEM (16-bit packed, 8 columns per K=16), B = V tile (MN-major)
+        auto issue_pv = [&](int t, int stage, bool accumulate) {
+          const uint32_t b0 = sV_addr + stage * L::kTileBytes;
+#pragma unroll
+          for (int kk = 0; kk < kBlockN / 16; ++kk) {
+            umma_ts(tmem_base + 256 + t * 128, tmem_base + t * 128 + kk * 8,
+                    make_smem_desc_sw128(b0 + kk * 2048, L::kSubTileBytes, 1024), idesc_pv,
+                    (accumulate || kk > 0) ? 1u : 0u);
+          }
+        };
+
+        if (nu > 0) {
+          mbar_wait(&k_full[0], 0);
+          tc_fence_after();
+#pragma unroll
+          for (int t = 0; t < kTilesPerCta; ++t) {
+            if (cnt[t] > 0) {
+              mbar_wait(&q_full[t], 0);
+              tc_fence_after();
+              issue_qk(t, 0);
+              umma_commit(&s_full[t]);
+            }
+          }
+          umma_commit(&k_empty[0]);
+        }
+        for (int u = 0; u < nu; ++u) {
+          const int s = u % ST;
+          const uint32_t ph = (u / ST) & 1;
+          const int s_next = (u + 1) % ST;
+          const uint32_t ph_next = ((u + 1) / ST) & 1;
+          mbar_wait(&v_full[s], ph);
+          bool k_next_ready = false;
+#pragma unroll
+          for (int t = 0; t < kTilesPerCta; ++t) {
+            if (u < cnt[t]) {
+              mbar_wait(&p_full[t], u & 1);
+              tc_fence_after();
+              issue_pv(t, s, u > 0);
+              if (u + 1 == cnt[t]) umma_commit(&o_full[t]);
+            }
+            if (u + 1 < cnt[t]) {
+              if (!k_next_ready) {
+                mbar_wait(&k_full[s_next], ph_next);
+                tc_fence_after();
+                k_next_ready = true;
+              }
+              issue_qk(t, s_next);
+              umma_commit(&s_full[t]);
+            }
+          }
+          umma_commit(&v_empty[s]);
+          if (u + 1 < nu) umma_commit(&k_empty[s_next]);
+        }
+      }
+    }
+  } else {
+    // ===================================== softmax warpgroups =================================
+    setmaxnreg_inc<kSoftmaxRegs>();
+    const int t = warp >> 2;
+    const int row_in_tile = (warp & 3) * 32 + lane;
+    const int qi = q0 + t * kBlockM + row_in_tile;          // query row within the sequence
+    const bool row_valid = qi < seq.seqlen_q;
+    const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
+    const uint32_t tS = tmem_base + lane_base + t * 128;
+    const uint32_t tO = tmem_base + lane_base + 256 + t * 128;
+    const float scale_log2 = p.softmax_scale * kLog2e;
+    const uint32_t bh = bidb * p.h + bidh;
+    const PhiloxKey pk = make_philox_key(p.philox_seed, p.philox_offset);
+    const uint32_t keep_thr = keep_threshold_u16(p.p_dropout);
+
+    float m = -INFINITY, l = 0.f;
+    const int my_cnt = cnt[t];
+    for (int u = 0; u < my_cnt; ++u) {
+      const int j = kSparse ? blk_list[u] : u;
+      mbar_wait(&s_full[t], u & 1);
+      tc_fence_after();
+      float sv[kBlockN];
+      {
+        uint32_t(&r)[4][32] = *reinterpret_cast<uint32_t(*)[4][32]>(sv);
+        tmem_ld32(tS + 0, r[0]);
+        tmem_ld32(tS + 32, r[1]);
+        tmem_ld32(tS + 64, r[2]);
+        tmem_ld32(tS + 96, r[3]);
+        tmem_wait_ld();
+      }
+      // ---- masking: key padding, causal (top-left aligned: key <= query), blocksparse ----
+      int limit = seq.seqlen_k - j * kBlockN;
+      if (kCausal) limit = min(limit, qi + 1 - j * kBlockN);
+      if (kSparse) { if (!bm.on(qi, j * kBlockN)) limit = 0; }
+      if (limit < kBlockN) {
+#pragma unroll
+        for (int c = 0; c < kBlockN; ++c)
+          if (c >= limit) sv[c] = -INFINITY;
+      }
+      // ---- row max ----
+      float mx0 = sv[0], mx1 = sv[1], mx2 = sv[2], mx3 = sv[3];
+#pragma unroll
+      for (int c = 4; c < kBlockN; c += 4) {
+        mx0 = fmaxf(mx0, sv[c]);
+        mx1 = fmaxf(mx1, sv[c + 1]);
+        mx2 = fmaxf(mx2, sv[c + 2]);
+        mx3 = fmaxf(mx3, sv[c + 3]);
+      }
+      const float m_blk = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+      // ---- lazy rescale of the running output (only when the max grew by more than 2^8) ----
+      if (u == 0) {
+        m = m_blk;
+      } else {
+        const bool need = (m_blk - m) * scale_log2 > kRescaleThreshold;   // false on NaN (-inf - -inf)
+        if (__any_sync(0xffffffffu, need)) {
+          const float m_new = fmaxf(m, m_blk);
+          const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+          const float alpha = ex2((m - m_use) * scale_log2);
+          l *= alpha;
+          m = m_new;
+#pragma unroll
+          for (int c4 = 0; c4 < DPAD / 32; ++c4) {
+            uint32_t o[32];
+            tmem_ld32(tO + c4 * 32, o);
+            tmem_wait_ld();
+#pragma unroll
+            for (int c = 0; c < 32; ++c) o[c] = __float_as_uint(__uint_as_float(o[c]) * alpha);
+            tmem_st32(tO + c4 * 32, o);
+          }
+        }
+      }
+      // ---- exponentials, row sum, dropout, pack to 16 bit ----
+      const float m_use = (m == -INFINITY) ? 0.f : m;
+      const float neg_ms = -m_use * scale_log2;
+      float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
+#pragma unroll
+      for (int c = 0; c < kBlockN; c += 4) {
+        sv[c] = ex2(fmaf(sv[c], scale_log2, neg_ms));
+        sv[c + 1] = ex2(fmaf(sv[c + 1], scale_log2, neg_ms));
+        sv[c + 2] = ex2(fmaf(sv[c + 2], scale_log2, neg_ms));
+        sv[c + 3] = ex2(fmaf(sv[c + 3], scale_log2, neg_ms));
+        sum0 += sv[c];
+        sum1 += sv[c + 1];
+        sum2 += sv[c + 2];
+        sum3 += sv[c + 3];
+      }
+      l += (sum0 + sum1) + (sum2 + sum3);
+      if (kDropout) {
+#pragma unroll
+        for (int g = 0; g < kBlockN / 8; ++g) {
+          const uint4 r = dropout_rand8(pk, bh, static_cast<uint32_t>(qi), static_cast<uint32_t>(j * (kBlockN / 8) + g));
+          const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            if ((w[e] & 0xFFFFu) > keep_thr) sv[g * 8 + 2 * e] = 0.f;
+            if ((w[e] >> 16) > keep_thr) sv[g * 8 + 2 * e + 1] = 0.f;
+          }
+        }
+      }
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        uint32_t pp[32];
+#pragma unroll
+        for (int c = 0; c < 32; ++c) pp[c] = pack2<kBf16>(sv[half * 64 + 2 * c], sv[half * 64 + 2 * c + 1]);
+        tmem_st32(tS + half * 32, pp);
+      }
+      tmem_wait_st();
+      tc_fence_before();
+      mbar_arrive(&p_full[t]);
+    }
+
+    // ---- epilogue: O = acc / l (x 1/keep), lse = m*scale + ln(l) ----
+    if (my_cnt > 0 || (q0 + t * kBlockM) < seq.seqlen_q) {
+      using T = typename Elem<kBf16>::T;
+      const bool dead = (l == 0.f) || (l != l);
+      const float inv_l = dead ? 1.f : 1.f / l;
+      const float out_scale = inv_l * (kDropout ? 1.f / (1.f - p.p_dropout) : 1.f);
+      const float lse = dead ? -INFINITY : (m * scale_log2 + log2f(l)) * kLn2;
+      T* orow = reinterpret_cast<T*>(p.o) + (int64_t)(seq.q_begin + qi) * p.o_row_stride + (int64_t)bidh * p.o_head_stride;
+      if (my_cnt > 0) {
+        mbar_wait(&o_full[t], 0);
+        tc_fence_after();
+      }
+#pragma unroll
+      for (int c4 = 0; c4 < DPAD / 32; ++c4) {
+        uint32_t o[32];
+        if (my_cnt > 0) {
+          tmem_ld32(tO + c4 * 32, o);
+          tmem_wait_ld();
+        } else {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) o[c] = 0u;
+        }
+        if (row_valid) {
+#pragma unroll
+          for (int v8 = 0; v8 < 4; ++v8) {
+            const int col = c4 * 32 + v8 * 8;
+            if (col < p.d) {
+              uint4 pk4;
+              pk4.x = pack2<kBf16>(__uint_as_float(o[v8 * 8 + 0]) * out_scale, __uint_as_float(o[v8 * 8 + 1]) * out_scale);
+              pk4.y = pack2<kBf16>(__uint_as_float(o[v8 * 8 + 2]) * out_scale, __uint_as_float(o[v8 * 8 + 3]) * out_scale);
+              pk4.z = pack2<kBf16>(__uint_as_float(o[v8 * 8 + 4]) * out_scale, __uint_as_float(o[v8 * 8 + 5]) * out_scale);
+              pk4.w = pack2<kBf16>(__uint_as_float(o[v8 * 8 + 6]) * out_scale, __uint_as_float(o[v8 * 8 + 7]) * out_scale);
+              *reinterpret_cast<uint4*>(orow + col) = pk4;
+            }
+          }
+        }
+      }
+      if (row_valid) p.softmax_lse[(int64_t)bh * p.seqlen_q_rounded + qi] = lse;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+PFN_cuTensorMapEncodeTiled_v12000 get_tensor_map_encoder() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  if (fn == nullptr) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(ptr);
+  }
+  return fn;
+}
+
+}  // namespace
+
+// (d, h, total) view of a packed (total, h, d) tensor with arbitrary row / head strides; box = 64 x 1 x rows,
+// 128-byte swizzle, out-of-bounds elements read as zero (this is what pads head dims to 64 / 128 and
+// clips the last rows of the packed batch).
+bool make_tensor_map_3d(CUtensorMap* map, const void* base, int d, int h, int64_t total, int64_t row_stride,
+                        int64_t head_stride, int box_rows) {
+  auto encode = get_tensor_map_encoder();
+  if (encode == nullptr) return false;
+  const cuuint64_t dims[3] = {static_cast<cuuint64_t>(d), static_cast<cuuint64_t>(h), static_cast<cuuint64_t>(total)};
+  const cuuint64_t strides[2] = {static_cast<cuuint64_t>(head_stride) * 2, static_cast<cuuint64_t>(row_stride) * 2};
+  const cuuint32_t box[3] = {64, 1, static_cast<cuuint32_t>(box_rows)};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  const CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_UINT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
+namespace {
+
+template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse>
+cudaError_t launch_fwd_variant(const FwdTensorMaps& maps, const fa_params& p, const BlockMaskView& bm, cudaStream_t stream) {
+  auto kernel = fwd_sm100_kernel<DPAD, kBf16, kCausal, kDropout, kSparse>;
+  constexpr int smem = FwdSmem<DPAD>::kDynamicBytes;
+  static bool configured[16] = {};   // per device
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 16 && !configured[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    configured[dev] = true;
+  } else if (dev >= 16) {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+  }
+  const dim3 grid((p.max_seqlen_q + kBlockM * kTilesPerCta - 1) / (kBlockM * kTilesPerCta), p.h, p.b);
+  kernel<<<grid, kNumThreads, smem, stream>>>(maps, p, bm);
+  return cudaGetLastError();
+}
+
+template <int DPAD, bool kBf16>
+cudaError_t dispatch_flags(const FwdTensorMaps& maps, const fa_params& p, const BlockMaskView& bm, cudaStream_t stream) {
+  const bool drop = p.p_dropout > 0.f;
+  if (bm.dense != nullptr) {
+    return drop ? launch_fwd_variant<DPAD, kBf16, false, true, true>(maps, p, bm, stream)
+                : launch_fwd_variant<DPAD, kBf16, false, false, true>(maps, p, bm, stream);
+  }
+  if (p.is_causal) {
+    return drop ? launch_fwd_variant<DPAD, kBf16, true, true, false>(maps, p, bm, stream)
+                : launch_fwd_variant<DPAD, kBf16, true, false, false>(maps, p, bm, stream);
+  }
+  return drop ? launch_fwd_variant<DPAD, kBf16, false, true, false>(maps, p, bm, stream)
+              : launch_fwd_variant<DPAD, kBf16, false, false, false>(maps, p, bm, stream);
+}
+
+}  // namespace
+
+// Head-dim dispatch mirrors run_fmha_fprop (src/fmha_fprop_kernel_dispatch.cu:90-134): d <= 64 -> 64, else 128.
+cudaError_t launch_fwd_sm100(const fa_params& p, const BlockMaskView& bm, cudaStream_t stream, const char** err_msg) {
+  *err_msg = nullptr;
+  if (p.max_seqlen_q <= 0 || p.total_q <= 0) return cudaSuccess;
+  if (bm.dense != nullptr && (p.max_seqlen_k + kBlockN - 1) / kBlockN > 512) {
+    *err_msg = "blocksparse forward supports at most 65536 keys per sequence";
+    return cudaErrorInvalidValue;
+  }
+  FwdTensorMaps maps;
+  // K/V tensors may be empty (total_k == 0): TMA needs a nonzero extent, the kernel then never issues a load.
+  const int64_t tk = p.total_k > 0 ? p.total_k : 1;
+  if (!make_tensor_map_3d(&maps.q, p.q, p.d, p.h, p.total_q, p.q_row_stride, p.q_head_stride, kBlockM) ||
+      !make_tensor_map_3d(&maps.k, p.k, p.d, p.h, tk, p.k_row_stride, p.k_head_stride, kBlockN) ||
+      !make_tensor_map_3d(&maps.v, p.v, p.d, p.h, tk, p.v_row_stride, p.v_head_stride, kBlockN)) {
+    *err_msg = "cuTensorMapEncodeTiled failed (q/k/v must be 16-byte aligned with 16-byte-multiple strides)";
+    return cudaErrorInvalidValue;
+  }
+  if (p.d <= 64) {
+    return p.is_bf16 ? dispatch_flags<64, true>(maps, p, bm, stream) : dispatch_flags<64, false>(maps, p, bm, stream);
+  }
+  return p.is_bf16 ? dispatch_flags<128, true>(maps, p, bm, stream) : dispatch_flags<128, false>(maps, p, bm, stream);
+}
+
+}  // namespace fa

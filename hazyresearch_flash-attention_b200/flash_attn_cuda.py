@@ -1,0 +1,338 @@
+"""`flash_attn_cuda` -- drop-in for the reference's pybind11 extension of the same name
+(reference: csrc/flash_attn/fmha_api.cpp:244-247 exports `fwd`; the Python layer additionally calls `bwd`,
+`fwd_block`, `bwd_block`: flash_attn/flash_attn_interface.py:19,31, flash_attn/flash_blocksparse_attn_interface.py:45,56).
+
+This module is a thin ctypes binding over the C-ABI library `csrc/libfa_b200.so` (include/fa_b200.h).  It does
+what `mha_fwd` does on the host (fmha_api.cpp:127-241): argument checks, output allocation, device guard,
+current stream, Philox (seed, offset) from the CUDA generator -- and nothing else.  There is no fallback of
+any kind: if the library is missing the import fails, and on a non-sm_100 device every call raises.
+"""
+import ctypes
+import math
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "csrc", "libfa_b200.so")
+
+FA_IMPL_AUTO, FA_IMPL_TCGEN05, FA_IMPL_SIMT = 0, 1, 2
+FA_OP_FWD, FA_OP_BWD, FA_OP_FWD_BLOCK, FA_OP_BWD_BLOCK = 0, 1, 2, 3
+
+# Kernel selection for debugging / cross-checks (FA_IMPL_*).  Tests flip this; users never need to.
+_impl = int(os.environ.get("FA_B200_IMPL", FA_IMPL_AUTO))
+
+
+def set_impl(impl):
+    global _impl
+    old, _impl = _impl, int(impl)
+    return old
+
+
+class FaParams(ctypes.Structure):
+    """Mirror of `struct fa_params` in include/fa_b200.h (field order and types must match)."""
+    _fields_ = (
+        [(n, ctypes.c_void_p) for n in (
+            "q", "k", "v", "o", "dout", "dq", "dk", "dv", "softmax_lse", "softmax_d", "s_dmask",
+            "cu_seqlens_q", "cu_seqlens_k", "blockmask", "workspace")]
+        + [("workspace_bytes", ctypes.c_uint64)]
+        + [(n, ctypes.c_int64) for n in (
+            "q_row_stride", "q_head_stride", "k_row_stride", "k_head_stride", "v_row_stride", "v_head_stride",
+            "o_row_stride", "o_head_stride", "do_row_stride", "do_head_stride", "dq_row_stride", "dq_head_stride",
+            "dk_row_stride", "dk_head_stride", "dv_row_stride", "dv_head_stride")]
+        + [(n, ctypes.c_int32) for n in (
+            "b", "h", "d", "total_q", "total_k", "max_seqlen_q", "max_seqlen_k", "seqlen_q_rounded",
+            "seqlen_k_rounded", "blockmask_nrow", "blockmask_ncol")]
+        + [("softmax_scale", ctypes.c_float), ("p_dropout", ctypes.c_float)]
+        + [(n, ctypes.c_int32) for n in ("is_causal", "is_bf16", "impl", "reserved0")]
+        + [("philox_seed", ctypes.c_uint64), ("philox_offset", ctypes.c_uint64)]
+    )
+
+
+def _load_library():
+    if not os.path.exists(_LIB_PATH):
+        raise ImportError(
+            f"{_LIB_PATH} not found: build it with `python __graft_entry__.py` (or `make -C "
+            f"{os.path.dirname(_LIB_PATH)}`).  flash_attn_cuda has no fallback path.")
+    lib = ctypes.CDLL(_LIB_PATH)
+    lib.fa_abi_version.restype = ctypes.c_int
+    lib.fa_last_error.restype = ctypes.c_char_p
+    lib.fa_workspace_bytes.restype = ctypes.c_uint64
+    lib.fa_workspace_bytes.argtypes = [ctypes.POINTER(FaParams), ctypes.c_int]
+    lib.fa_philox_increment.restype = ctypes.c_uint64
+    lib.fa_philox_increment.argtypes = [ctypes.POINTER(FaParams)]
+    for name in ("fa_fwd", "fa_bwd", "fa_fwd_block", "fa_bwd_block"):
+        fn = getattr(lib, name)
+        fn.restype = ctypes.c_int
+        fn.argtypes = [ctypes.POINTER(FaParams), ctypes.c_void_p]
+    for name in ("fa_gather_rows", "fa_scatter_rows"):
+        fn = getattr(lib, name)
+        fn.restype = ctypes.c_int
+        fn.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64,
+                       ctypes.c_void_p]
+    lib.fa_dropout_keep8_host.restype = None
+    lib.fa_dropout_keep8_host.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint32,
+                                          ctypes.c_uint32, ctypes.c_float, ctypes.c_void_p]
+    if lib.fa_abi_version() != 1:
+        raise ImportError(f"{_LIB_PATH}: ABI version {lib.fa_abi_version()} != 1")
+    lib.fa_sizeof_params.restype = ctypes.c_uint64
+    if lib.fa_sizeof_params() != ctypes.sizeof(FaParams):
+        raise ImportError(f"{_LIB_PATH}: sizeof(fa_params) = {lib.fa_sizeof_params()} but the ctypes mirror has "
+                          f"{ctypes.sizeof(FaParams)} bytes")
+    return lib
+
+
+_lib = _load_library()
+
+
+def _check(cond, msg):
+    if not cond:
+        raise RuntimeError(msg)
+
+
+def _raise_if_failed(rc, what):
+    if rc != 0:
+        raise RuntimeError(f"{what} failed (code {rc}): {_lib.fa_last_error().decode()}")
+
+
+def _ptr(t):
+    return t.data_ptr() if t is not None else None
+
+
+def _round_multiple(x, m):
+    return (x + m - 1) // m * m
+
+
+def seqlen_k_rounded(max_seqlen_k, head_size):
+    """Column extent of S_dmask.  Same rule as the reference host code for a non-sm80 device
+    (fmha_api.cpp:172-179): K blocks of 128 when the padded head dim is 128, else 256."""
+    blocksize_c = 128 if head_size > 64 else 256
+    if max_seqlen_k <= 128:
+        return 128
+    if max_seqlen_k <= 256:
+        return 256
+    return _round_multiple(max_seqlen_k, blocksize_c)
+
+
+def _check_qkv(q, k, v, cu_seqlens_q, cu_seqlens_k):
+    # the TORCH_CHECKs of fmha_api.cpp:135-170
+    _check(q.is_cuda and k.is_cuda and v.is_cuda, "q, k, v must be CUDA tensors")
+    _check(q.dtype in (torch.float16, torch.bfloat16), "q must be fp16 or bf16")
+    _check(k.dtype == q.dtype and v.dtype == q.dtype, "q, k, v must have the same dtype")
+    _check(cu_seqlens_q.dtype == torch.int32 and cu_seqlens_k.dtype == torch.int32, "cu_seqlens must be int32")
+    _check(cu_seqlens_q.is_cuda and cu_seqlens_k.is_cuda, "cu_seqlens must be CUDA tensors")
+    _check(q.dim() == 3 and k.dim() == 3 and v.dim() == 3, "q, k, v must be (total, nheads, headdim)")
+    _check(q.stride(-1) == 1 and k.stride(-1) == 1 and v.stride(-1) == 1, "last dim of q, k, v must be contiguous")
+    _check(cu_seqlens_q.is_contiguous() and cu_seqlens_k.is_contiguous(), "cu_seqlens must be contiguous")
+    batch_size = cu_seqlens_q.numel() - 1
+    _check(batch_size > 0, "batch size must be positive")
+    total_q, num_heads, head_size = q.shape
+    total_k = k.shape[0]
+    _check(head_size % 8 == 0 and head_size <= 128, "head dim must be a multiple of 8 and at most 128")
+    _check(tuple(k.shape) == (total_k, num_heads, head_size), "k has the wrong shape")
+    _check(tuple(v.shape) == (total_k, num_heads, head_size), "v has the wrong shape")
+    _check(cu_seqlens_k.numel() == batch_size + 1, "cu_seqlens_k has the wrong shape")
+    return batch_size, total_q, total_k, num_heads, head_size
+
+
+def _philox_state(p_dropout, gen, device, params):
+    """(seed, offset) for this call; advances the generator like at::CUDAGeneratorImpl::philox_cuda_state
+    (fmha_api.cpp:228-235).  No RNG state is touched when p_dropout == 0 (fmha_api.cpp:231)."""
+    if p_dropout <= 0.0:
+        return 0, 0
+    if gen is None:
+        idx = device.index if device.index is not None else torch.cuda.current_device()
+        gen = torch.cuda.default_generators[idx]
+    seed = gen.initial_seed()
+    offset = gen.get_offset()
+    gen.set_offset(offset + int(_lib.fa_philox_increment(ctypes.byref(params))))
+    return seed & 0xFFFFFFFFFFFFFFFF, offset
+
+
+def _fill_common(P, q, k, v, cu_seqlens_q, cu_seqlens_k, b, h, d, total_q, total_k, max_seqlen_q, max_seqlen_k,
+                 p_dropout, softmax_scale, is_causal):
+    P.q, P.k, P.v = _ptr(q), _ptr(k), _ptr(v)
+    P.q_row_stride, P.q_head_stride = q.stride(0), q.stride(1)
+    P.k_row_stride, P.k_head_stride = k.stride(0), k.stride(1)
+    P.v_row_stride, P.v_head_stride = v.stride(0), v.stride(1)
+    P.cu_seqlens_q, P.cu_seqlens_k = _ptr(cu_seqlens_q), _ptr(cu_seqlens_k)
+    P.b, P.h, P.d, P.total_q, P.total_k = b, h, d, total_q, total_k
+    P.max_seqlen_q, P.max_seqlen_k = max_seqlen_q, max_seqlen_k
+    P.seqlen_q_rounded = _round_multiple(max_seqlen_q, 16)
+    P.seqlen_k_rounded = seqlen_k_rounded(max_seqlen_k, d)
+    P.softmax_scale, P.p_dropout = softmax_scale, p_dropout
+    P.is_causal = 1 if is_causal else 0
+    P.is_bf16 = 1 if q.dtype == torch.bfloat16 else 0
+    P.impl = _impl
+
+
+def _workspace(P, op, device):
+    nbytes = int(_lib.fa_workspace_bytes(ctypes.byref(P), op))
+    if nbytes == 0:
+        return None
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=device)
+    P.workspace, P.workspace_bytes = ws.data_ptr(), nbytes
+    return ws
+
+
+def _fwd_impl(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, p_dropout, softmax_scale,
+              zero_tensors, is_causal, return_softmax, gen, blockmask=None):
+    b, total_q, total_k, h, d = _check_qkv(q, k, v, cu_seqlens_q, cu_seqlens_k)
+    _check(p_dropout < 1.0, "p_dropout must be < 1")
+    P = FaParams()
+    _fill_common(P, q, k, v, cu_seqlens_q, cu_seqlens_k, b, h, d, total_q, total_k, int(max_seqlen_q),
+                 int(max_seqlen_k), float(p_dropout), float(softmax_scale), is_causal)
+    with torch.cuda.device(q.device):
+        o = torch.empty((total_q, h, d), dtype=q.dtype, device=q.device)
+        lse = torch.empty((b, h, P.seqlen_q_rounded), dtype=torch.float32, device=q.device)
+        s = None
+        if return_softmax:
+            # zero-filled: the kernel writes only (row < seqlen_q, col < seqlen_k) entries
+            s = torch.zeros((b, h, P.seqlen_q_rounded, P.seqlen_k_rounded), dtype=q.dtype, device=q.device)
+            P.s_dmask = s.data_ptr()
+        if zero_tensors:   # fmha_api.cpp:199-203
+            o.zero_()
+            lse.fill_(-math.inf)
+        P.o, P.o_row_stride, P.o_head_stride = o.data_ptr(), o.stride(0), o.stride(1)
+        P.softmax_lse = lse.data_ptr()
+        op = FA_OP_FWD
+        if blockmask is not None:
+            _check(blockmask.dtype == torch.int32 and blockmask.is_cuda and blockmask.is_contiguous()
+                   and blockmask.dim() == 2, "blockmask must be a contiguous 2-D int32 CUDA tensor (converted format)")
+            P.blockmask = blockmask.data_ptr()
+            P.blockmask_ncol, P.blockmask_nrow = blockmask.shape
+            op = FA_OP_FWD_BLOCK
+        ws = _workspace(P, op, q.device)
+        P.philox_seed, P.philox_offset = _philox_state(p_dropout, gen, q.device, P)
+        stream = torch.cuda.current_stream().cuda_stream
+        fn = _lib.fa_fwd if blockmask is None else _lib.fa_fwd_block
+        _raise_if_failed(fn(ctypes.byref(P), stream), "flash_attn_cuda.fwd")
+        if ws is not None:
+            ws.record_stream(torch.cuda.current_stream())
+    return [o, lse] + ([s] if return_softmax else [])
+
+
+def _bwd_impl(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seqlens_k, max_seqlen_q,
+              max_seqlen_k, p_dropout, softmax_scale, zero_tensors, is_causal, gen, blockmask=None):
+    b, total_q, total_k, h, d = _check_qkv(q, k, v, cu_seqlens_q, cu_seqlens_k)
+    _check(dout.is_cuda and out.is_cuda and dq.is_cuda and dk.is_cuda and dv.is_cuda, "all tensors must be CUDA")
+    for name, t, shape in (("dout", dout, (total_q, h, d)), ("out", out, (total_q, h, d)),
+                           ("dq", dq, (total_q, h, d)), ("dk", dk, (total_k, h, d)), ("dv", dv, (total_k, h, d))):
+        _check(t.dtype == q.dtype, f"{name} must have the dtype of q")
+        _check(tuple(t.shape) == shape, f"{name} has the wrong shape")
+    _check(softmax_lse.dtype == torch.float32 and softmax_lse.is_contiguous(), "softmax_lse must be contiguous fp32")
+    _check(dq.stride(-1) == 1 and dk.stride(-1) == 1 and dv.stride(-1) == 1, "last dim of dq, dk, dv must be contiguous")
+    if dout.stride(-1) != 1:
+        dout = dout.contiguous()
+    if out.stride(-1) != 1:
+        out = out.contiguous()
+    P = FaParams()
+    _fill_common(P, q, k, v, cu_seqlens_q, cu_seqlens_k, b, h, d, total_q, total_k, int(max_seqlen_q),
+                 int(max_seqlen_k), float(p_dropout), float(softmax_scale), is_causal)
+    _check(tuple(softmax_lse.shape) == (b, h, P.seqlen_q_rounded), "softmax_lse has the wrong shape")
+    with torch.cuda.device(q.device):
+        softmax_d = torch.empty((b, h, P.seqlen_q_rounded), dtype=torch.float32, device=q.device)
+        if zero_tensors:
+            dq.zero_(), dk.zero_(), dv.zero_(), softmax_d.zero_()
+        P.o, P.o_row_stride, P.o_head_stride = out.data_ptr(), out.stride(0), out.stride(1)
+        P.dout, P.do_row_stride, P.do_head_stride = dout.data_ptr(), dout.stride(0), dout.stride(1)
+        P.dq, P.dq_row_stride, P.dq_head_stride = dq.data_ptr(), dq.stride(0), dq.stride(1)
+        P.dk, P.dk_row_stride, P.dk_head_stride = dk.data_ptr(), dk.stride(0), dk.stride(1)
+        P.dv, P.dv_row_stride, P.dv_head_stride = dv.data_ptr(), dv.stride(0), dv.stride(1)
+        P.softmax_lse, P.softmax_d = softmax_lse.data_ptr(), softmax_d.data_ptr()
+        op = FA_OP_BWD
+        if blockmask is not None:
+            P.blockmask = blockmask.data_ptr()
+            P.blockmask_ncol, P.blockmask_nrow = blockmask.shape
+            op = FA_OP_BWD_BLOCK
+        ws = _workspace(P, op, q.device)
+        P.philox_seed, P.philox_offset = _philox_state(p_dropout, gen, q.device, P)
+        stream = torch.cuda.current_stream().cuda_stream
+        fn = _lib.fa_bwd if blockmask is None else _lib.fa_bwd_block
+        _raise_if_failed(fn(ctypes.byref(P), stream), "flash_attn_cuda.bwd")
+        if ws is not None:
+            ws.record_stream(torch.cuda.current_stream())
+    return softmax_d
+
+
+# ---------------------------------------------------------------------------------------------------
+# the four entry points of the reference extension, same positional signatures
+# ---------------------------------------------------------------------------------------------------
+def fwd(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, p_dropout, softmax_scale,
+        zero_tensors, is_causal, return_softmax, gen=None):
+    """-> [o (total_q, h, d), softmax_lse (b, h, round16(max_seqlen_q)) fp32 (, s_dmask)].
+    Signature of mha_fwd, fmha_api.cpp:112-125.  s_dmask deviates from the reference's MMA-fragment layout:
+    it is the natural (b, h, sq_rounded, sk_rounded) matrix of +-P with P = exp(scale*s - lse) (true
+    probabilities), sign bit set where the position was dropped."""
+    return _fwd_impl(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, p_dropout,
+                     softmax_scale, zero_tensors, is_causal, return_softmax, gen)
+
+
+def bwd(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k,
+        p_dropout, softmax_scale, zero_tensors, is_causal, gen=None):
+    """Writes dq, dk, dv in place (any row/head stride) and returns softmax_d = rowsum(dO*O).
+    Call site: flash_attn/flash_attn_interface.py:31-33."""
+    return _bwd_impl(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seqlens_k, max_seqlen_q,
+                     max_seqlen_k, p_dropout, softmax_scale, zero_tensors, is_causal, gen)
+
+
+def _check_qkv_packed(qkv, blockmask):
+    _check(qkv.dim() == 4 and qkv.shape[1] == 3, "qkv must be (total, 3, nheads, headdim)")
+    _check(blockmask.dim() == 2, "blockmask must be 2-D (converted format, see convert_blockmask)")
+
+
+def fwd_block(qkv, cu_seqlens, blockmask, p_dropout, max_s, softmax_scale, is_causal, return_softmax, gen=None):
+    """-> [context, softmax_lse (, S_dmask)].  Call site: flash_attn/flash_blocksparse_attn_interface.py:45-47.
+    `blockmask` is the converted (ncol, nrow) int32 mask of convert_blockmask."""
+    _check_qkv_packed(qkv, blockmask)
+    return _fwd_impl(qkv[:, 0], qkv[:, 1], qkv[:, 2], cu_seqlens, cu_seqlens, max_s, max_s, p_dropout,
+                     softmax_scale, False, is_causal, return_softmax, gen, blockmask=blockmask)
+
+
+def bwd_block(dout, qkv, out, S_dmask, softmax_lse, cu_seqlens, blockmask, p_dropout, softmax_scale, max_s,
+              is_causal, gen=None):
+    """-> (dqkv, dp, softmax_d).  Call site: flash_attn/flash_blocksparse_attn_interface.py:56-58 (note the
+    argument order differs from fwd_block).  S_dmask is accepted for signature compatibility and unused (the
+    dropout mask is regenerated from the Philox stream).  dp is a debug tensor in the reference; here None."""
+    _check_qkv_packed(qkv, blockmask)
+    dqkv = torch.empty_like(qkv)
+    softmax_d = _bwd_impl(dout, qkv[:, 0], qkv[:, 1], qkv[:, 2], out, softmax_lse, dqkv[:, 0], dqkv[:, 1],
+                          dqkv[:, 2], cu_seqlens, cu_seqlens, max_s, max_s, p_dropout, softmax_scale, False,
+                          is_causal, gen, blockmask=blockmask)
+    return dqkv, None, softmax_d
+
+
+# ---------------------------------------------------------------------------------------------------
+# varlen pack / unpack kernels used by flash_attn.bert_padding
+# ---------------------------------------------------------------------------------------------------
+def gather_rows(src2d, indices):
+    """out[i] = src2d[indices[i]]; src2d (n, w) contiguous CUDA, indices int64 CUDA."""
+    _check(src2d.is_cuda and indices.is_cuda and src2d.dim() == 2 and src2d.is_contiguous(), "bad gather input")
+    _check(indices.dtype == torch.int64 and indices.is_contiguous(), "indices must be contiguous int64")
+    out = torch.empty((indices.numel(), src2d.shape[1]), dtype=src2d.dtype, device=src2d.device)
+    row_bytes = src2d.shape[1] * src2d.element_size()
+    with torch.cuda.device(src2d.device):
+        rc = _lib.fa_gather_rows(_ptr(out), _ptr(src2d), _ptr(indices), indices.numel(), row_bytes,
+                                 torch.cuda.current_stream().cuda_stream)
+    _raise_if_failed(rc, "fa_gather_rows")
+    return out
+
+
+def scatter_rows(src2d, indices, first_axis_dim):
+    """out = zeros(first_axis_dim, w); out[indices[i]] = src2d[i]."""
+    _check(src2d.is_cuda and indices.is_cuda and src2d.dim() == 2 and src2d.is_contiguous(), "bad scatter input")
+    _check(indices.dtype == torch.int64 and indices.is_contiguous(), "indices must be contiguous int64")
+    out = torch.zeros((first_axis_dim, src2d.shape[1]), dtype=src2d.dtype, device=src2d.device)
+    row_bytes = src2d.shape[1] * src2d.element_size()
+    with torch.cuda.device(src2d.device):
+        rc = _lib.fa_scatter_rows(_ptr(out), _ptr(src2d), _ptr(indices), indices.numel(), row_bytes,
+                                  torch.cuda.current_stream().cuda_stream)
+    _raise_if_failed(rc, "fa_scatter_rows")
+    return out
+
+
+def dropout_keep8_host(seed, offset, bh, qrow, kgroup, p_dropout):
+    """CPU evaluation of the dropout stream (tests only): keep flags of keys 8*kgroup..8*kgroup+7."""
+    buf = (ctypes.c_uint8 * 8)()
+    _lib.fa_dropout_keep8_host(seed, offset, bh, qrow, kgroup, p_dropout, buf)
+    return [bool(x) for x in buf]

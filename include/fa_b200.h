@@ -1,0 +1,132 @@
+/* fa_b200.h -- C ABI of libfa_b200.so, the B200 (sm_100a) replacement for the reference's
+ * `flash_attn_cuda` native extension on the attention hot path.
+ *
+ * Every entry point below replaces one native call the reference's Python layer binds
+ * (paths relative to the reference repo):
+ *
+ *   fa_fwd        <- flash_attn_cuda.fwd        csrc/flash_attn/fmha_api.cpp:112-242 (mha_fwd),
+ *                                               called at flash_attn/flash_attn_interface.py:19-22
+ *   fa_bwd        <- flash_attn_cuda.bwd        called at flash_attn/flash_attn_interface.py:31-33
+ *                                               (native source absent from the reference snapshot)
+ *   fa_fwd_block  <- flash_attn_cuda.fwd_block  called at flash_attn/flash_blocksparse_attn_interface.py:45-47
+ *   fa_bwd_block  <- flash_attn_cuda.bwd_block  called at flash_attn/flash_blocksparse_attn_interface.py:56-58
+ *   fa_gather_rows / fa_scatter_rows            the torch.gather / scatter_ / index_put the reference issues in
+ *                                               flash_attn/bert_padding.py:21-22, 30-35, 48-53, 59
+ *
+ * Conventions: plain pointers and sizes only (no torch types); all data pointers are DEVICE pointers;
+ * strides are in ELEMENTS; the library never allocates device memory and never synchronises the host --
+ * work is enqueued on `stream` (a cudaStream_t passed as void*).  Every function returns 0 on success and
+ * a nonzero FA_ERR_* code otherwise; fa_last_error() gives the message for the calling thread.
+ * Argument errors correspond to the TORCH_CHECKs of fmha_api.cpp:127-170.
+ */
+#ifndef FA_B200_H_
+#define FA_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FA_B200_ABI_VERSION 1
+
+enum {
+  FA_OK = 0,
+  FA_ERR_INVALID_ARGUMENT = 1, /* shape / dtype / stride / alignment violations */
+  FA_ERR_UNSUPPORTED_DEVICE = 2, /* device is not compute capability 10.x */
+  FA_ERR_CUDA = 3,             /* a CUDA runtime / driver call failed */
+  FA_ERR_WORKSPACE = 4         /* workspace missing or too small */
+};
+
+/* kernel selection (fa_params.impl) */
+enum {
+  FA_IMPL_AUTO = 0,   /* tcgen05/TMA kernels (the product path) */
+  FA_IMPL_TCGEN05 = 1,
+  FA_IMPL_SIMT = 2    /* CUDA-core cross-check kernels: bring-up / debugging only */
+};
+
+/* Mirrors Qkv_params + FMHA_fprop_params of the reference (csrc/flash_attn/src/fmha.h:50-124),
+ * with 64-bit strides (the reference's 32-bit strides limit tensors to 2 GB, fmha.h:59-60). */
+typedef struct fa_params {
+  /* --- device pointers ------------------------------------------------------------------- */
+  const void* q;            /* (total_q, h, d) */
+  const void* k;            /* (total_k, h, d) */
+  const void* v;            /* (total_k, h, d) */
+  void* o;                  /* (total_q, h, d): fwd output, bwd input */
+  const void* dout;         /* bwd: (total_q, h, d) */
+  void* dq;                 /* bwd outputs, caller-allocated, fully overwritten */
+  void* dk;
+  void* dv;
+  float* softmax_lse;       /* (b, h, seqlen_q_rounded) fp32, natural log; fwd output, bwd input */
+  float* softmax_d;         /* bwd output (b, h, seqlen_q_rounded) fp32 = rowsum(dO * O) */
+  void* s_dmask;            /* optional debug output (b, h, seqlen_q_rounded, seqlen_k_rounded), same dtype as q:
+                               +P kept / -P dropped, P = exp(scale*s - lse)  (NULL = not requested) */
+  const int32_t* cu_seqlens_q; /* (b + 1) */
+  const int32_t* cu_seqlens_k; /* (b + 1) */
+  const int32_t* blockmask; /* blocksparse only: converted mask (ncol, nrow) int32, see
+                               flash_blocksparse_attn_interface.py:8-40; NULL for dense */
+  void* workspace;          /* scratch, size >= fa_workspace_bytes() */
+  uint64_t workspace_bytes;
+
+  /* --- strides, in elements (last dim must be contiguous) --------------------------------- */
+  int64_t q_row_stride, q_head_stride;
+  int64_t k_row_stride, k_head_stride;
+  int64_t v_row_stride, v_head_stride;
+  int64_t o_row_stride, o_head_stride;
+  int64_t do_row_stride, do_head_stride;
+  int64_t dq_row_stride, dq_head_stride;
+  int64_t dk_row_stride, dk_head_stride;
+  int64_t dv_row_stride, dv_head_stride;
+
+  /* --- sizes ------------------------------------------------------------------------------ */
+  int32_t b, h, d;
+  int32_t total_q, total_k;
+  int32_t max_seqlen_q, max_seqlen_k;          /* caller's upper bounds */
+  int32_t seqlen_q_rounded, seqlen_k_rounded;  /* row / col extents of softmax_lse, softmax_d, s_dmask */
+  int32_t blockmask_nrow, blockmask_ncol;      /* blocksparse: nrow = S/16 blocks, ncol = S/256 blocks */
+
+  /* --- scalars ---------------------------------------------------------------------------- */
+  float softmax_scale;
+  float p_dropout;          /* probability of DROPPING, in [0, 1) */
+  int32_t is_causal;        /* top-left aligned: key j visible to query i iff j <= i */
+  int32_t is_bf16;          /* 0 = fp16, 1 = bf16 */
+  int32_t impl;             /* FA_IMPL_* */
+  int32_t reserved0;
+  uint64_t philox_seed;     /* dropout RNG stream (position keyed: identical in fwd, bwd and s_dmask) */
+  uint64_t philox_offset;
+} fa_params;
+
+enum { FA_OP_FWD = 0, FA_OP_BWD = 1, FA_OP_FWD_BLOCK = 2, FA_OP_BWD_BLOCK = 3 };
+
+int fa_abi_version(void);
+uint64_t fa_sizeof_params(void);   /* sizeof(fa_params): lets a foreign-language binding verify its struct mirror */
+const char* fa_last_error(void);
+
+/* bytes of scratch `op` needs for these sizes (0 if none). Pure host arithmetic. */
+uint64_t fa_workspace_bytes(const fa_params* p, int op);
+/* how far the caller must advance its Philox offset after a call with dropout (fmha_api.cpp:228-234). */
+uint64_t fa_philox_increment(const fa_params* p);
+
+int fa_fwd(const fa_params* p, void* stream);
+int fa_bwd(const fa_params* p, void* stream);
+int fa_fwd_block(const fa_params* p, void* stream);
+int fa_bwd_block(const fa_params* p, void* stream);
+
+/* Varlen pack / unpack (bert_padding.py).  Rows are `row_bytes` long (multiple of 4 bytes).
+ * gather : dst[i, :] = src[indices[i], :]             for i in [0, n_indices)
+ * scatter: dst[indices[i], :] = src[i, :]             (dst rows not named by indices are left untouched)
+ * indices are int64 (torch.nonzero output). */
+int fa_gather_rows(void* dst, const void* src, const int64_t* indices, int64_t n_indices, int64_t row_bytes,
+                   void* stream);
+int fa_scatter_rows(void* dst, const void* src, const int64_t* indices, int64_t n_indices, int64_t row_bytes,
+                    void* stream);
+
+/* Host-only helper exposing the dropout RNG for tests: fills keep[8] (0/1) for the 8 key positions
+ * 8*kgroup .. 8*kgroup+7 of query row `qrow` in (batch*h + head) = bh.  Pure CPU code. */
+void fa_dropout_keep8_host(uint64_t seed, uint64_t offset, uint32_t bh, uint32_t qrow, uint32_t kgroup,
+                           float p_dropout, uint8_t* keep);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FA_B200_H_ */
