@@ -1,0 +1,206 @@
+"""CPU tests (no GPU needed): the oracle against fixtures produced by the reference's own Python code
+(tests/golden/make_golden.py), the host-side logic of the drop-in package, and the C-ABI library's exports."""
+import ctypes
+import math
+import os
+import re
+
+import pytest
+import torch
+
+import fa_test_utils as U
+from oracle import attention_ref as orc
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB = os.path.join(ROOT, "hazyresearch_flash-attention_b200", "csrc", "libfa_b200.so")
+HEADER = os.path.join(ROOT, "include", "fa_b200.h")
+
+ATTN_CASES = U.load_golden("attention_ref_cases.pt")
+BS_CASES = U.load_golden("blocksparse_cases.pt")
+
+
+@pytest.mark.parametrize("idx", range(len(ATTN_CASES)))
+def test_oracle_matches_reference_attention_ref(idx):
+    c = ATTN_CASES[idx]
+    dmask = U.unpack_bool(c["dmask"])
+    q, k, v = [c[n].clone().requires_grad_() for n in ("q", "k", "v")]
+    out, attn = orc.attention_ref(q, k, v, c["qmask"], c["kmask"], c["p"], dmask, causal=c["causal"])
+    # same math, same op order, same dtype -> bitwise equal on the same CPU build; allow 1 ulp of the dtype
+    tol = 2e-3 if c["dtype"] == "torch.float16" else 1.6e-2
+    assert (out.float() - c["out_ref"].float()).abs().max().item() <= tol * max(1.0, c["out_ref"].float().abs().max().item())
+    if c["attn_ref"] is not None:
+        assert (attn.float() - c["attn_ref"].float()).abs().max().item() <= tol
+    dq, dk, dv = torch.autograd.grad(out, (q, k, v), c["dout"])
+    for got, ref in ((dq, c["dq"]), (dk, c["dk"]), (dv, c["dv"])):
+        assert (got.float() - ref.float()).abs().max().item() <= tol * max(1.0, ref.float().abs().max().item())
+    out_pt, _ = orc.attention_ref(c["q"], c["k"], c["v"], c["qmask"], c["kmask"], c["p"], dmask, causal=c["causal"],
+                                  upcast=False, reorder_ops=True)
+    pt_err = (out_pt.float() - out.float()).abs().max().item()
+    assert abs(pt_err - c["out_pt_maxerr"]) <= 0.5 * c["out_pt_maxerr"] + 1e-6
+    frac = orc.get_dropout_fraction(dmask, c["qmask"], c["kmask"], causal=c["causal"]).item()
+    assert abs(frac - c["dropout_fraction"]) < 1e-6
+
+
+def test_oracle_none_dropout_mask_is_keep_all():
+    c = ATTN_CASES[0]
+    a, _ = orc.attention_ref(c["q"], c["k"], c["v"], c["qmask"], c["kmask"], 0.0, None, causal=c["causal"])
+    ones = torch.ones(c["b"], c["h"], c["sq"], c["sk"], dtype=torch.bool)
+    b, _ = orc.attention_ref(c["q"], c["k"], c["v"], c["qmask"], c["kmask"], 0.0, ones, causal=c["causal"])
+    assert torch.equal(a, b)
+
+
+def test_oracle_lse_consistent_with_attention():
+    c = ATTN_CASES[1]
+    lse = orc.softmax_lse_ref(c["q"], c["k"], c["qmask"], c["kmask"], c["causal"])
+    q, k = c["q"].float(), c["k"].float()
+    scores = torch.einsum("bthd,bshd->bhts", q / math.sqrt(c["d"]), k)
+    _, attn = orc.attention_ref(c["q"], c["k"], c["v"], None, c["kmask"], 0.0, None, causal=c["causal"])
+    recon = torch.exp(scores - lse[..., None])
+    vis = attn.float() > 0
+    assert (recon[vis] - attn.float()[vis]).abs().max().item() < 2e-3
+
+
+@pytest.mark.parametrize("idx", range(len(BS_CASES["attn"])))
+def test_oracle_matches_reference_blocksparse_ref(idx):
+    c = BS_CASES["attn"][idx]
+    dmask = U.unpack_bool(c["dmask"])
+    out, attn = orc.attention_blocksparse_ref(c["qkv"], c["blockmask"], c["amask"], c["p"], dmask)
+    assert (out.float() - c["out"].float()).abs().max().item() <= 2e-3
+    if c["attn"] is not None:
+        assert (attn.float() - c["attn"].float()).abs().max().item() <= 1e-3
+
+
+@pytest.mark.parametrize("idx", range(len(BS_CASES["convert"])))
+def test_convert_blockmask_matches_reference(idx):
+    from flash_attn.flash_blocksparse_attn_interface import convert_blockmask
+    c = BS_CASES["convert"][idx]
+    got = convert_blockmask(c["blockmask"], causal=False)
+    assert got.dtype == torch.int32
+    assert torch.equal(got, c["converted"])
+    assert torch.equal(orc.convert_blockmask_ref(c["blockmask"]), c["converted"])
+
+
+def test_convert_blockmask_rejects_causal():
+    from flash_attn.flash_blocksparse_attn_interface import convert_blockmask
+    with pytest.raises(AssertionError):
+        convert_blockmask(torch.ones(16, 1), causal=True)
+
+
+def test_butterfly_layout():
+    from flash_attn.flash_blocksparse_attention import ButterflySparsityConfig
+    lay = ButterflySparsityConfig().make_layout(2048)
+    assert tuple(lay.shape) == (128, 8)
+    assert torch.equal(lay.bool(), orc.butterfly_blockmask(2048))
+    blocks = lay[::16].bool()
+    assert torch.equal(blocks, blocks.T) and bool(blocks.diagonal().all())
+    assert blocks.sum().item() == 8 * (1 + 3)   # self + log2(8) partners
+
+
+def test_bert_padding_matches_reference_cpu():
+    from flash_attn.bert_padding import pad_input, unpad_input
+    for c in U.load_golden("bert_padding_cases.pt"):
+        x = c["x"].clone().requires_grad_()
+        xu, idx, cu, mx = unpad_input(x, c["mask"])
+        assert torch.equal(xu, c["x_unpad"]) and torch.equal(idx, c["indices"])
+        assert torch.equal(cu, c["cu_seqlens"]) and cu.dtype == torch.int32 and mx == c["max_seqlen"]
+        back = pad_input(xu, idx, x.shape[0], x.shape[1])
+        assert torch.equal(back, c["repadded"])
+        back.sum().backward()   # gather bwd (scatter) o scatter bwd (gather)
+        assert torch.equal(x.grad, c["mask"][..., None].expand_as(x).to(x.dtype))
+
+
+def test_index_first_axis_residual_cpu():
+    from flash_attn.bert_padding import index_first_axis_residual
+    x = torch.randn(10, 3, 4, requires_grad=True)
+    idx = torch.tensor([7, 2, 5])
+    out, res = index_first_axis_residual(x, idx)
+    assert torch.equal(out, x[idx]) and torch.equal(res, x)
+    (out.sum() + 2 * res.sum()).backward()
+    expect = torch.full_like(x, 2.0)
+    expect[idx] += 1.0
+    assert torch.equal(x.grad, expect)
+
+
+def test_rotary_matches_reference():
+    from flash_attn.rotary import RotaryEmbedding, RotaryEmbedding2D
+    c = U.load_golden("rotary_cases.pt")
+    q1, k1 = RotaryEmbedding(32)(c["q"], c["k"], seq_dimension=-3)
+    q2, k2 = RotaryEmbedding2D(32)(c["q"], c["k"], seq_dimension=-3)
+    for got, ref in ((q1, c["q1"]), (k1, c["k1"]), (q2, c["q2"]), (k2, c["k2"])):
+        assert torch.allclose(got, ref, atol=1e-6, rtol=1e-6)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# C-ABI library: loads without a GPU and exports every symbol the header declares
+# ------------------------------------------------------------------------------------------------------------
+def _declared_symbols():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(fa_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    assert os.path.exists(LIB), "build the library first: python __graft_entry__.py"
+    lib = ctypes.CDLL(LIB)
+    names = _declared_symbols()
+    assert {"fa_fwd", "fa_bwd", "fa_fwd_block", "fa_bwd_block", "fa_gather_rows", "fa_scatter_rows",
+            "fa_last_error", "fa_workspace_bytes", "fa_philox_increment"} <= set(names)
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/fa_b200.h but not exported"
+
+
+def test_shim_struct_mirror_and_host_helpers():
+    import flash_attn_cuda
+    assert flash_attn_cuda._lib.fa_sizeof_params() == ctypes.sizeof(flash_attn_cuda.FaParams)
+    P = flash_attn_cuda.FaParams()
+    P.p_dropout = 0.1
+    assert flash_attn_cuda._lib.fa_philox_increment(ctypes.byref(P)) == 4
+    P.p_dropout = 0.0
+    assert flash_attn_cuda._lib.fa_philox_increment(ctypes.byref(P)) == 0
+    P.blockmask_nrow, P.blockmask_ncol = 128, 8
+    assert flash_attn_cuda._lib.fa_workspace_bytes(ctypes.byref(P), flash_attn_cuda.FA_OP_FWD_BLOCK) == 1024
+    assert flash_attn_cuda.seqlen_k_rounded(97, 64) == 128 and flash_attn_cuda.seqlen_k_rounded(200, 64) == 256
+    assert flash_attn_cuda.seqlen_k_rounded(257, 64) == 512 and flash_attn_cuda.seqlen_k_rounded(257, 128) == 384
+
+
+def test_invalid_arguments_are_rejected_without_a_gpu():
+    import flash_attn_cuda
+    P = flash_attn_cuda.FaParams()
+    rc = flash_attn_cuda._lib.fa_fwd(ctypes.byref(P), None)
+    assert rc == 1 and b"batch size" in flash_attn_cuda._lib.fa_last_error()
+    P.b, P.h, P.d = 1, 1, 12
+    rc = flash_attn_cuda._lib.fa_fwd(ctypes.byref(P), None)
+    assert rc == 1 and b"head dim" in flash_attn_cuda._lib.fa_last_error()
+    q = torch.zeros(4, 1, 8, dtype=torch.float16)
+    cu = torch.tensor([0, 4], dtype=torch.int32)
+    with pytest.raises(RuntimeError):   # CPU tensors: the product path has no CPU fallback
+        flash_attn_cuda.fwd(q, q, q, cu, cu, 4, 4, 0.0, 1.0, False, False, False, None)
+
+
+def test_dropout_stream_statistics_host():
+    """The position-keyed Philox stream (integer work, evaluated on the host) keeps ~(1-p) of positions."""
+    import flash_attn_cuda
+    p = 0.17
+    kept = total = 0
+    for row in range(64):
+        for g in range(64):
+            keep = flash_attn_cuda.dropout_keep8_host(1234, 8, 3, row, g, p)
+            kept += sum(keep)
+            total += 8
+    assert abs((1 - kept / total) / p - 1.0) < 0.03
+    a = flash_attn_cuda.dropout_keep8_host(1, 0, 0, 5, 7, 0.5)
+    assert a == flash_attn_cuda.dropout_keep8_host(1, 0, 0, 5, 7, 0.5)
+    assert a != flash_attn_cuda.dropout_keep8_host(1, 4, 0, 5, 7, 0.5) or a != flash_attn_cuda.dropout_keep8_host(2, 0, 0, 5, 7, 0.5)
+    assert all(flash_attn_cuda.dropout_keep8_host(1, 0, 0, 5, 7, 0.0))
+
+
+def test_package_resolves_into_repo():
+    import flash_attn
+    import flash_attn_cuda
+    assert flash_attn.__file__.startswith(ROOT) and flash_attn_cuda.__file__.startswith(ROOT)
+    from flash_attn.flash_attn_interface import (flash_attn_func, flash_attn_unpadded_func,  # noqa: F401
+                                                 flash_attn_unpadded_kvpacked_func,
+                                                 flash_attn_unpadded_qkvpacked_func, _get_block_size)
+    from flash_attn.flash_attention import FlashAttention, FlashMHA   # noqa: F401
+    from flash_attn.flash_blocksparse_attn_interface import flash_blocksparse_attn_func   # noqa: F401
+    from flash_attn.flash_blocksparse_attention import FlashBlocksparseAttention, FlashBlocksparseMHA   # noqa: F401
