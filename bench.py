@@ -1,0 +1,345 @@
+"""bench.py -- attention fwd+bwd throughput on B200 (BASELINE.json metric), one JSON line on stdout.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload d128|d64] [--sweep]
+
+A "step" is one forward+backward pass of the attention hot path over one synthetic batch, through the public API
+(flash_attn_unpadded_qkvpacked_func -> flash_attn_cuda -> libfa_b200.so).  N > 1: one process per GPU (torchrun),
+the (batch x heads) units are sharded with no data-path collective (weak scaling: every rank runs the full
+per-GPU workload); time = max over ranks.
+FLOP model: F_fwd = 4*b*h*sq*sk*d (/2 causal), F_bwd = 2.5*F_fwd, F_fwd+bwd = 3.5*F_fwd.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (os.path.join(ROOT, "hazyresearch_flash-attention_b200"), ROOT):
+    if _p in sys.path:
+        sys.path.remove(_p)
+    sys.path.insert(0, _p)
+
+import torch  # noqa: E402
+
+WORKLOADS = {
+    # BASELINE.json configs[2] / north_star target: head dim 128 bf16 b16 h12, seqlen >= 4K, causal
+    "d128": dict(b=16, h=12, d=128, s=4096, causal=True, p=0.0, dtype="bf16",
+                 name="b16 h12 d128 S4096 causal bf16 fwd+bwd (BASELINE configs[2], north_star target)"),
+    # BASELINE.json configs[1]: GPT-2 causal fp16 b8 h12 d64, dropout 0.1
+    "d64": dict(b=8, h=12, d=64, s=4096, causal=True, p=0.1, dtype="fp16",
+                name="b8 h12 d64 S4096 causal fp16 dropout 0.1 fwd+bwd (BASELINE configs[1])"),
+    # BASELINE.json configs[0]: BERT-base non-causal S512
+    "bert": dict(b=8, h=12, d=64, s=512, causal=False, p=0.0, dtype="fp16",
+                 name="b8 h12 d64 S512 non-causal fp16 fwd+bwd (BASELINE configs[0])"),
+}
+
+
+def flops_fwd(b, h, sq, sk, d, causal):
+    f = 4.0 * b * h * sq * sk * d
+    return f / 2 if causal else f
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        pk = json.load(open(path))
+        return dict(burst=pk["bf16_tflops"], sustained=pk["bf16_tflops_sustained"], hbm=pk["hbm_gbs"], src="measured")
+    return dict(burst=1590.0, sustained=1400.0, hbm=6650.0, src="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clock / throttle-reason samples during the timed region (B200_PROFILING.md recipe)."""
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.FIELDS}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def make_batch(w, device, seed):
+    dtype = torch.bfloat16 if w["dtype"] == "bf16" else torch.float16
+    g = torch.Generator(device=device).manual_seed(seed)
+    total = w["b"] * w["s"]
+    qkv = torch.randn(total, 3, w["h"], w["d"], device=device, dtype=dtype, generator=g)
+    dout = torch.randn(total, w["h"], w["d"], device=device, dtype=dtype, generator=g)
+    cu = torch.arange(0, (w["b"] + 1) * w["s"], w["s"], device=device, dtype=torch.int32)
+    return qkv, dout, cu
+
+
+def cpu_reference_step(w, sample_b, sample_h):
+    """The reference's 'PyTorch standard attention' (oracle port of attention_ref, fp32) fwd+bwd on host cores."""
+    from oracle import attention_ref as orc
+    g = torch.Generator().manual_seed(0)
+    q, k, v = [torch.randn(sample_b, w["s"], sample_h, w["d"], generator=g).requires_grad_() for _ in range(3)]
+    dout = torch.randn(sample_b, w["s"], sample_h, w["d"], generator=g)
+
+    def step():
+        keep = None
+        if w["p"] > 0:
+            keep = torch.rand(sample_b, sample_h, w["s"], w["s"]) >= w["p"]
+        out, _ = orc.attention_ref(q, k, v, None, None, w["p"], keep, causal=w["causal"])
+        torch.autograd.grad(out, (q, k, v), dout)
+    return step, 3.5 * flops_fwd(sample_b, sample_h, w["s"], w["s"], w["d"], w["causal"])
+
+
+def run_reference(args, w):
+    """--impl reference: the reference's own CPU implementation of the path (oracle port; the reference's CUDA
+    kernels do not run on cc 10.0), all host threads, each step a bounded sample of the workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    torch.set_num_threads(os.cpu_count() or 1)
+    sample_b, sample_h = 1, 2
+    step, flops = cpu_reference_step(w, sample_b, sample_h)
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = (time.perf_counter() - t0) / args.steps
+    val = flops / dt / 1e12
+    sample = f"b={sample_b} h={sample_h} slice of the workload's (b{w['b']}, h{w['h']}) units, fp32, per step"
+    line = {"impl": "reference", "metric": "attn fwd+bwd TFLOP/s per GPU", "value": val, "unit": "TFLOP/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
+            "config": {"workload": w["name"], "sample": sample},
+            "cpu_baseline": {"value": val, "unit": "TFLOP/s", "cores": torch.get_num_threads(), "kind": "port",
+                             "sample": sample},
+            "e2e": {"value": val, "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, w):
+    import flash_attn_cuda
+    from flash_attn.flash_attn_interface import flash_attn_unpadded_qkvpacked_func
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    qkv, dout, cu = make_batch(w, device, seed=1234 + rank)   # every rank owns its own (batch x heads) units
+    qkv.requires_grad_()
+    s, p, causal = w["s"], w["p"], w["causal"]
+    f_fwd = flops_fwd(w["b"], w["h"], s, s, w["d"], causal)
+    f_step = 3.5 * f_fwd
+    in_bytes = qkv.numel() * qkv.element_size() + dout.numel() * dout.element_size()
+
+    def step():
+        out = flash_attn_unpadded_qkvpacked_func(qkv, cu, s, p, causal=causal)
+        dqkv, = torch.autograd.grad(out, qkv, dout)
+        return out, dqkv
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+
+    # ---- timed region: K steps, inputs resident in HBM; per-kernel-group events on the launching stream ----
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+    launches0 = flash_attn_cuda._lib.fa_launch_count()
+    barrier()
+    t_start = torch.cuda.Event(enable_timing=True)
+    t_end = torch.cuda.Event(enable_timing=True)
+    t_start.record()
+    for i in range(args.steps):
+        ev[i][0].record()
+        out = flash_attn_unpadded_qkvpacked_func(qkv, cu, s, p, causal=causal)
+        ev[i][1].record()
+        torch.autograd.grad(out, qkv, dout)
+        ev[i][2].record()
+    t_end.record()
+    barrier()
+    launches = flash_attn_cuda._lib.fa_launch_count() - launches0
+    clocks = sampler.stop() if sampler else None
+    ms_total = t_start.elapsed_time(t_end)
+    fwd_ms = sum(e[0].elapsed_time(e[1]) for e in ev) / args.steps
+    bwd_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / args.steps
+
+    # ---- end-to-end: host buffers in, host buffers out, copies inside the timed region ----
+    qkv_h = qkv.detach().cpu().pin_memory()
+    dout_h = dout.cpu().pin_memory()
+    out_h = torch.empty_like(dout_h).pin_memory()
+    dqkv_h = torch.empty_like(qkv_h).pin_memory()
+    qkv_d = torch.empty_like(qkv_h, device=device).requires_grad_()
+    dout_d = torch.empty_like(dout_h, device=device)
+
+    def e2e_step():
+        with torch.no_grad():
+            qkv_d.copy_(qkv_h, non_blocking=True)
+            dout_d.copy_(dout_h, non_blocking=True)
+        o = flash_attn_unpadded_qkvpacked_func(qkv_d, cu, s, p, causal=causal)
+        g, = torch.autograd.grad(o, qkv_d, dout_d)
+        out_h.copy_(o.detach(), non_blocking=True)
+        dqkv_h.copy_(g, non_blocking=True)
+
+    e2e_steps = max(2, min(args.steps, 5))
+    e2e_step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(e2e_steps):
+        e2e_step()
+    e1.record()
+    barrier()
+    e2e_ms = e0.elapsed_time(e1) / e2e_steps
+
+    times = torch.tensor([ms_total, e2e_ms], device=device, dtype=torch.float64)
+    if dist is not None:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    ms_step = times[0].item() / args.steps
+    e2e_ms = times[1].item()
+
+    if rank == 0:
+        peaks = load_peaks()
+        long_region = times[0].item() > 1000.0
+        peak = peaks["sustained"] if long_region else peaks["burst"]
+        dom = "bwd" if bwd_ms >= fwd_ms else "fwd"
+        dom_flops = 2.5 * f_fwd if dom == "bwd" else f_fwd
+        dom_ms = bwd_ms if dom == "bwd" else fwd_ms
+        achieved = dom_flops / (dom_ms * 1e-3) / 1e12
+        value = world * f_step / (ms_step * 1e-3) / 1e12
+        line = {
+            "metric": "attn fwd+bwd TFLOP/s per GPU", "value": value, "unit": "TFLOP/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": w["dtype"], "data": "synthetic",
+            "config": {"workload": w["name"], "global_batch": w["b"] * world, "seq_len": s,
+                       "parallelism": f"(batch x heads) units sharded over {world} GPU(s), no collective",
+                       "l2": f"inputs {in_bytes / 2**20:.0f} MiB per GPU > 126 MB L2 (no flush needed)",
+                       "per_gpu_tflops": value / world, "fwd_ms": fwd_ms, "bwd_ms": bwd_ms,
+                       "fwd_tflops": f_fwd / (fwd_ms * 1e-3) / 1e12, "bwd_tflops": 2.5 * f_fwd / (bwd_ms * 1e-3) / 1e12,
+                       "frac_of_bf16_peak_fwd_bwd": value / world / peak},
+            "roofline": {"bound": "tensor", "kernel": f"{dom} ({'tcgen05' if dom == 'fwd' else 'see DESIGN.md'})",
+                         "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                         "peak_source": f"{peaks['src']} {'sustained' if long_region else 'burst'} bf16 matmul",
+                         "traffic": None},
+            "e2e": {"value": world * f_step / (e2e_ms * 1e-3) / 1e12, "unit": "TFLOP/s", "ms_per_step": e2e_ms,
+                    "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": in_bytes},
+            "gpu_launches": int(launches), "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            torch.set_num_threads(os.cpu_count() or 1)
+            sb, sh = 1, 2
+            cstep, cflops = cpu_reference_step(w, sb, sh)
+            cstep()
+            best = 1e30
+            t_all = time.perf_counter()
+            while True:
+                t0 = time.perf_counter()
+                cstep()
+                best = min(best, time.perf_counter() - t0)
+                if time.perf_counter() - t_all > 10.0:
+                    break
+            line["cpu_baseline"] = {"value": cflops / best / 1e12, "unit": "TFLOP/s", "cores": torch.get_num_threads(),
+                                    "kind": "port",
+                                    "sample": f"b={sb} h={sh} slice of the workload, fp32 attention_ref fwd+bwd, best step in 10 s"}
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def run_sweep(args):
+    """fwd / bwd / fwd+bwd TFLOP/s vs seqlen for both BASELINE shapes (one line per point, to stdout)."""
+    from flash_attn.flash_attn_interface import flash_attn_unpadded_qkvpacked_func
+    device = torch.device("cuda", 0)
+    peaks = load_peaks()
+    pts = [("d64", dict(b=8, h=12, d=64, dtype="fp16", p=0.1), [512, 1024, 2048, 4096]),
+           ("d128", dict(b=16, h=12, d=128, dtype="bf16", p=0.0), [512, 1024, 2048, 4096, 8192, 16384])]
+    for tag, base, seqs in pts:
+        for s in seqs:
+            if s > args.max_seqlen:
+                continue
+            for causal in (False, True):
+                w = dict(base, s=s, causal=causal)
+                qkv, dout, cu = make_batch(w, device, 0)
+                qkv.requires_grad_()
+                ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+                reps = 5
+                for it in range(2):
+                    n = 2 if it == 0 else reps
+                    torch.cuda.synchronize()
+                    tf = tb = 0.0
+                    for _ in range(n):
+                        ev[0].record()
+                        out = flash_attn_unpadded_qkvpacked_func(qkv, cu, s, w["p"], causal=causal)
+                        ev[1].record()
+                        if not args.fwd_only:
+                            torch.autograd.grad(out, qkv, dout)
+                        ev[2].record()
+                        torch.cuda.synchronize()
+                        tf += ev[0].elapsed_time(ev[1])
+                        tb += ev[1].elapsed_time(ev[2])
+                tf, tb = tf / reps, max(tb / reps, 1e-9)
+                f = flops_fwd(w["b"], w["h"], s, s, w["d"], causal)
+                print(json.dumps({"sweep": tag, "seqlen": s, "causal": causal, "dropout": w["p"],
+                                  "fwd_ms": tf, "bwd_ms": tb, "fwd_tflops": f / tf / 1e9, "bwd_tflops": 2.5 * f / tb / 1e9,
+                                  "fwd_bwd_tflops": 3.5 * f / (tf + tb) / 1e9,
+                                  "frac_burst_peak": 3.5 * f / (tf + tb) / 1e9 / peaks["burst"]}), flush=True)
+                del qkv, dout
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="d128", choices=sorted(WORKLOADS))
+    ap.add_argument("--sweep", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--fwd-only", action="store_true", help="sweep: time the forward only")
+    ap.add_argument("--max-seqlen", type=int, default=16384, help="sweep: largest seqlen")
+    args = ap.parse_args()
+    w = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, w)
+    elif args.sweep:
+        run_sweep(args)
+    else:
+        run_ours(args, w)
+
+
+if __name__ == "__main__":
+    main()

@@ -6,6 +6,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <atomic>
 
 #include "fa_common.cuh"
 #include "fa_kernels.h"
@@ -156,6 +157,7 @@ int move_rows(void* dst, const void* src, const int64_t* indices, int64_t n, int
     if (kGather) gather_rows_kernel<uint32_t><<<grid, threads, 0, st>>>((uint32_t*)dst, (const uint32_t*)src, indices, n, vecs);
     else scatter_rows_kernel<uint32_t><<<grid, threads, 0, st>>>((uint32_t*)dst, (const uint32_t*)src, indices, n, vecs);
   }
+  count_launch();
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return cuda_fail(e, kGather ? "gather_rows launch" : "scatter_rows launch");
   return FA_OK;
@@ -239,9 +241,14 @@ int run_bwd(const fa_params* p, void* stream, bool block) {
 
 }  // namespace
 
+static std::atomic<unsigned long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+unsigned long long launches_so_far() { return g_launches.load(std::memory_order_relaxed); }
+
 cudaError_t launch_expand_blockmask(const int32_t* converted, int nrow, int ncol, uint8_t* dense, cudaStream_t stream) {
   const int n = nrow * ncol;
   expand_blockmask_kernel<<<(n + 255) / 256, 256, 0, stream>>>(converted, nrow, ncol, dense);
+  count_launch();
   return cudaGetLastError();
 }
 
@@ -256,6 +263,7 @@ extern "C" {
 int fa_abi_version(void) { return FA_B200_ABI_VERSION; }
 uint64_t fa_sizeof_params(void) { return sizeof(fa_params); }
 const char* fa_last_error(void) { return fa::g_last_error; }
+uint64_t fa_launch_count(void) { return fa::launches_so_far(); }
 
 uint64_t fa_workspace_bytes(const fa_params* p, int op) {
   if (p == nullptr) return 0;

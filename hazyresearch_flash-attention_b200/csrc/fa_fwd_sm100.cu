@@ -470,6 +470,7 @@ cudaError_t launch_fwd_variant(const FwdTensorMaps& maps, const fa_params& p, co
   }
   const dim3 grid((p.max_seqlen_q + kBlockM * kTilesPerCta - 1) / (kBlockM * kTilesPerCta), p.h, p.b);
   kernel<<<grid, kNumThreads, smem, stream>>>(maps, p, bm);
+  count_launch();
   return cudaGetLastError();
 }
 

@@ -6,6 +6,9 @@
 
 namespace fa {
 
+// every kernel launch of the library bumps this (fa_launch_count() in the C ABI)
+void count_launch();
+
 // --- CUDA-core cross-check kernels (fa_simt.cu) ---
 cudaError_t launch_simt_fwd(const fa_params& p, const BlockMaskView& bm, bool only_sdmask, cudaStream_t stream);
 cudaError_t launch_simt_bwd(const fa_params& p, const BlockMaskView& bm, cudaStream_t stream);

@@ -323,7 +323,7 @@ cudaError_t launch_simt_fwd(const fa_params& p, const BlockMaskView& bm, bool on
   if (p.max_seqlen_q <= 0) return cudaSuccess;
   const dim3 grid = row_grid(p.max_seqlen_q, p);
   if (p.is_bf16) simt_fwd_kernel<true><<<grid, kWarpsPerCta * 32, 0, stream>>>(p, bm, only_sdmask ? 1 : 0);
-  else simt_fwd_kernel<false><<<grid, kWarpsPerCta * 32, 0, stream>>>(p, bm, only_sdmask ? 1 : 0);
+  else simt_fwd_kernel<false><<<grid, kWarpsPerCta * 32, 0, stream>>>(p, bm, only_sdmask ? 1 : 0); count_launch();
   return cudaGetLastError();
 }
 
@@ -331,7 +331,7 @@ cudaError_t launch_dot_do_o(const fa_params& p, cudaStream_t stream) {
   if (p.seqlen_q_rounded <= 0) return cudaSuccess;
   const dim3 grid = row_grid(p.seqlen_q_rounded, p);
   if (p.is_bf16) simt_dot_do_o_kernel<true><<<grid, kWarpsPerCta * 32, 0, stream>>>(p);
-  else simt_dot_do_o_kernel<false><<<grid, kWarpsPerCta * 32, 0, stream>>>(p);
+  else simt_dot_do_o_kernel<false><<<grid, kWarpsPerCta * 32, 0, stream>>>(p); count_launch();
   return cudaGetLastError();
 }
 
@@ -341,14 +341,14 @@ cudaError_t launch_simt_bwd(const fa_params& p, const BlockMaskView& bm, cudaStr
   if (p.max_seqlen_q > 0) {
     const dim3 grid = row_grid(p.max_seqlen_q, p);
     if (p.is_bf16) simt_bwd_dq_kernel<true><<<grid, kWarpsPerCta * 32, 0, stream>>>(p, bm);
-    else simt_bwd_dq_kernel<false><<<grid, kWarpsPerCta * 32, 0, stream>>>(p, bm);
+    else simt_bwd_dq_kernel<false><<<grid, kWarpsPerCta * 32, 0, stream>>>(p, bm); count_launch();
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
   }
   if (p.max_seqlen_k > 0) {
     const dim3 grid = row_grid(p.max_seqlen_k, p);
     if (p.is_bf16) simt_bwd_dkv_kernel<true><<<grid, kWarpsPerCta * 32, 0, stream>>>(p, bm);
-    else simt_bwd_dkv_kernel<false><<<grid, kWarpsPerCta * 32, 0, stream>>>(p, bm);
+    else simt_bwd_dkv_kernel<false><<<grid, kWarpsPerCta * 32, 0, stream>>>(p, bm); count_launch();
     e = cudaGetLastError();
   }
   return e;

@@ -76,6 +76,7 @@ def _load_library():
     if lib.fa_abi_version() != 1:
         raise ImportError(f"{_LIB_PATH}: ABI version {lib.fa_abi_version()} != 1")
     lib.fa_sizeof_params.restype = ctypes.c_uint64
+    lib.fa_launch_count.restype = ctypes.c_uint64
     if lib.fa_sizeof_params() != ctypes.sizeof(FaParams):
         raise ImportError(f"{_LIB_PATH}: sizeof(fa_params) = {lib.fa_sizeof_params()} but the ctypes mirror has "
                           f"{ctypes.sizeof(FaParams)} bytes")

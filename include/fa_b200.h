@@ -101,6 +101,8 @@ enum { FA_OP_FWD = 0, FA_OP_BWD = 1, FA_OP_FWD_BLOCK = 2, FA_OP_BWD_BLOCK = 3 };
 int fa_abi_version(void);
 uint64_t fa_sizeof_params(void);   /* sizeof(fa_params): lets a foreign-language binding verify its struct mirror */
 const char* fa_last_error(void);
+/* number of CUDA kernels this library has launched in this process (monotonic; for benchmarks' launch accounting) */
+uint64_t fa_launch_count(void);
 
 /* bytes of scratch `op` needs for these sizes (0 if none). Pure host arithmetic. */
 uint64_t fa_workspace_bytes(const fa_params* p, int op);
