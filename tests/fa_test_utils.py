@@ -84,6 +84,11 @@ def decode_s_dmask(S_dmask, seqlen_q, seqlen_k):
     sign bit set = dropped.  (The reference needs convert_flash_attn_S_to_softmax + normalize_flash_attn_S,
     tests/test_flash_attn.py:218-297, to undo its MMA-fragment layout and per-block scaling.)"""
     S = S_dmask[:, :, :seqlen_q, :seqlen_k]
+    # the kernel's extents are round-ups of max_seqlen, which can be smaller than the padded test length:
+    # pad with +0 (probability 0, "kept") like the reference's converter does (tests/test_flash_attn.py:253-260)
+    pad_q, pad_k = seqlen_q - S.shape[2], seqlen_k - S.shape[3]
+    if pad_q > 0 or pad_k > 0:
+        S = torch.nn.functional.pad(S, (0, max(pad_k, 0), 0, max(pad_q, 0)))
     dropout_mask = ~torch.signbit(S.float())
     return dropout_mask, S.abs()
 
