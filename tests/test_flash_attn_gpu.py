@@ -148,8 +148,11 @@ def test_flash_attn_unpadded(seqlen, d, dropout_p, causal, dtype):
         check_2x(name, got, ref, pt)
     # softmax_lse: natural-log LSE of the scaled masked scores (documented at flash_attn_interface.py:168-170)
     lse_ref = orc.softmax_lse_ref(q, k, qmask, kmask, causal)
-    ok = qmask[:, None, :].expand_as(lse_ref) & torch.isfinite(lse_ref)
-    assert (lse[:, :, :seqlen] - lse_ref)[ok].abs().max().item() < 2e-3
+    # lse has round16(max_seqlen_q) columns, which can be fewer than the padded test length (e.g. 96 < 97)
+    n = min(seqlen, lse.shape[2])
+    assert not bool(qmask[:, n:].any())
+    ok = (qmask[:, None, :].expand_as(lse_ref) & torch.isfinite(lse_ref))[:, :, :n]
+    assert (lse[:, :, :n] - lse_ref[:, :, :n])[ok].abs().max().item() < 2e-3
 
 
 @pytest.mark.parametrize("dtype", DTYPES)
