@@ -234,7 +234,8 @@ int run_bwd(const fa_params* p, void* stream, bool block) {
     return fail(FA_ERR_WORKSPACE, "workspace too small: need %llu bytes, have %llu", (unsigned long long)need,
                 (unsigned long long)p->workspace_bytes);
   const char* msg = nullptr;
-  cudaError_t e = launch_bwd_sm100(*p, bm, st, &msg);
+  void* bwd_ws = static_cast<uint8_t*>(p->workspace) + (block ? blockmask_bytes(p) : 0);
+  cudaError_t e = launch_bwd_sm100(*p, bm, bwd_ws, st, &msg);
   if (e != cudaSuccess) return msg ? fail(FA_ERR_INVALID_ARGUMENT, "%s", msg) : cuda_fail(e, "tcgen05 backward launch");
   return FA_OK;
 }

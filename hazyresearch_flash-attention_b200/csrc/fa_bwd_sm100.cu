@@ -1,16 +1,738 @@
-// FlashAttention backward for sm_100a (tcgen05 / TMA).  INTERIM: until the tcgen05 backward lands the AUTO
-// path runs the CUDA-core kernels of fa_simt.cu (still a GPU path inside this library -- never a CPU or
-// library fallback).
+// FlashAttention backward for sm_100a: TMA -> shared memory -> tcgen05.mma with TMEM accumulators.
+// Replaces the native `bwd` / `bwd_block` the reference's Python layer binds (flash_attn/flash_attn_interface.py:31-33,
+// flash_attn/flash_blocksparse_attn_interface.py:56-58; native source absent from the reference snapshot).  The math is
+// the autograd of attention_ref (tests/test_flash_attn.py:141-155):
+//     P = exp(scale*S - lse)   dV = (P o Z / keep)^T dO   dP = (dO V^T) o Z / keep   dS = P o (dP - D)
+//     D = rowsum(dO o O)       dQ = scale * dS K          dK = scale * dS^T Q
+//
+// Three launches:  preprocess (D, -lse*log2e, per row)  ->  main  ->  postprocess (dQ fp32 accumulator -> 16 bit).
+//
+// Main kernel: one CTA owns a block of 128 keys (K and V tiles stay in shared memory) and streams 128-row Q / dO tiles.
+// Everything the softmax-side threads touch is computed TRANSPOSED (keys on TMEM lanes, queries on TMEM columns):
+//     S^T  = K Q^T      (SS MMA)      P^T -> TMEM (16 bit, aliases S^T)      dV += P^T dO   (TS MMA, A from TMEM)
+//     dP^T = V dO^T     (SS MMA)      dS^T -> shared memory (16 bit)         dK += dS^T Q   (SS MMA)
+//                                                                            dQ  = dS K     (SS MMA, both operands MN-major)
+// dQ tiles are drained TMEM -> registers -> shared memory and added into an fp32 accumulator in global memory with
+// cp.reduce.async.bulk (one 8 KB bulk reduction per 16 head-dim columns); the postprocess kernel scales and converts it.
+// TMEM columns: S^T/P^T [0,128) | dP^T, then dQ [128,256) | dV [256,256+DPAD) | dK [384,384+DPAD).
+// Warps: 0-7 compute (warpgroup g handles query columns 64g..64g+63 of every tile), 8-11 dQ drain, 12 MMA issuer,
+// 13 TMA loader, 14-15 idle.
+#include <cudaTypedefs.h>
+
 #include "fa_common.cuh"
 #include "fa_kernels.h"
+#include "sm100_ptx.cuh"
 
 namespace fa {
 
-uint64_t bwd_sm100_workspace_bytes(const fa_params& p) { (void)p; return 0; }
+namespace {
 
-cudaError_t launch_bwd_sm100(const fa_params& p, const BlockMaskView& bm, cudaStream_t stream, const char** err_msg) {
+constexpr int kBM = 128;            // queries per tile
+constexpr int kBN = 128;            // keys per CTA
+constexpr int kBwdThreads = 512;
+constexpr int kComputeRegs = 176;
+constexpr int kDrainRegs = 96;
+constexpr int kOtherRegs = 64;
+constexpr int kMaxSparseTiles = 512;
+
+template <int DPAD>
+struct BwdSmem {
+  static constexpr int kTile = 128 * DPAD * 2;            // one [128 x DPAD] 16-bit tile
+  static constexpr int kSub = 128 * 128;                  // [128 rows x 64 cols] swizzle-128B sub tile
+  static constexpr int kKOff = 0;
+  static constexpr int kVOff = kKOff + kTile;
+  static constexpr int kQOff = kVOff + kTile;             // 2 stages
+  static constexpr int kDoOff = kQOff + 2 * kTile;        // 1 stage
+  static constexpr int kDsOff = kDoOff + kTile;           // dS^T: [128 keys x 128 queries] 16 bit
+  static constexpr int kDqOff = kDsOff + 2 * kSub;        // dQ staging: 2 x 8 KB
+  static constexpr int kDqStageBytes = 8192;
+  static constexpr int kStatOff = kDqOff + 2 * kDqStageBytes;   // 2 stages x { -lse*log2e [128], D [128] } fp32
+  static constexpr int kMaskOff = kStatOff + 2 * 1024;    // dropout keep bits: 2 x [4 key words][128 queries] u32
+  static constexpr int kListOff = kMaskOff + 2 * 2048;    // blocksparse: int16 list[512], uint8 flags[512]
+  static constexpr int kBarOff = kListOff + kMaxSparseTiles * 3;
+  static constexpr int kNumBars = 16;
+  static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
+  static constexpr int kTotal = kTmemPtrOff + 16;
+  static constexpr int kDynamicBytes = kTotal + 1024;     // + alignment slack
+};
+static_assert(BwdSmem<128>::kDynamicBytes <= 232448, "shared memory budget");
+
+struct BwdTensorMaps {
+  CUtensorMap q, k, v, dout;
+};
+
+struct BwdWs {
+  float* nl;         // (b*h, sq_pad): -lse*log2e, -inf for rows that must produce P = 0
+  float* dsum;       // (b*h, sq_pad): D = rowsum(dO o O), 0 for invalid rows
+  float* dq_accum;   // (b*h, n_qtiles, DPAD/4, 128, 4) fp32
+  int sq_pad, n_qtiles;
+};
+
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+// ------------------------------------------------------------------------------------------------
+// main kernel
+// ------------------------------------------------------------------------------------------------
+template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse>
+__global__ void __launch_bounds__(kBwdThreads, 1)
+bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, const BlockMaskView bm, const BwdWs ws) {
+  using L = BwdSmem<DPAD>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int bidb = blockIdx.z, bidh = blockIdx.y, n_blk = blockIdx.x;
+  const SeqInfo seq(p.cu_seqlens_q, p.cu_seqlens_k, bidb);
+  const int k0 = n_blk * kBN;
+  if (k0 >= seq.seqlen_k) return;   // CTA-uniform: no key rows to produce
+  const uint32_t bh = bidb * p.h + bidh;
+
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
+  uint64_t* k_full = bars + 0;
+  uint64_t* v_full = bars + 1;
+  uint64_t* q_full = bars + 2;    // [2]
+  uint64_t* q_empty = bars + 4;   // [2]
+  uint64_t* do_full = bars + 6;
+  uint64_t* do_empty = bars + 7;
+  uint64_t* s_full = bars + 8;
+  uint64_t* dp_full = bars + 9;
+  uint64_t* p_full = bars + 10;
+  uint64_t* ds_full = bars + 11;
+  uint64_t* ds_empty = bars + 12;
+  uint64_t* dq_full = bars + 13;
+  uint64_t* dq_empty = bars + 14;
+  uint64_t* dkv_full = bars + 15;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + L::kTmemPtrOff);
+  int16_t* tile_list = reinterpret_cast<int16_t*>(smem + L::kListOff);
+  uint8_t* tile_flags = smem + L::kListOff + kMaxSparseTiles * 2;
+  __shared__ int s_num_active;
+
+  // Q tiles this CTA visits
+  const int n_qt_total = (seq.seqlen_q + kBM - 1) / kBM;
+  const int m_start = kCausal ? n_blk : 0;    // top-left aligned causal: queries >= first key of the block
+  int n_iter = max(n_qt_total - m_start, 0);
+
+  if (kSparse) {
+    const int c = k0 >> 8;
+    for (int m = threadIdx.x; m < n_qt_total; m += kBwdThreads) {
+      uint32_t f = 0;
+      if (c < bm.ncol) {
+#pragma unroll
+        for (int g = 0; g < 8; ++g) {
+          const int r = m * 8 + g;
+          if (r < bm.nrow && bm.dense[r * bm.ncol + c] != 0) f |= 1u << g;
+        }
+      }
+      tile_flags[m] = static_cast<uint8_t>(f);
+    }
+    __syncthreads();
+    if (warp == 0) {
+      int n_act = 0;
+      for (int m0 = 0; m0 < n_qt_total; m0 += 32) {
+        const int m = m0 + lane;
+        const bool f = m < n_qt_total && tile_flags[m] != 0;
+        const uint32_t ball = __ballot_sync(0xffffffffu, f);
+        if (f) tile_list[n_act + __popc(ball & ((1u << lane) - 1))] = static_cast<int16_t>(m);
+        n_act += __popc(ball);
+      }
+      if (lane == 0) s_num_active = n_act;
+    }
+    __syncthreads();
+    n_iter = s_num_active;
+  }
+  auto tile_of = [&](int it) -> int { return kSparse ? static_cast<int>(tile_list[it]) : m_start + it; };
+
+  if (threadIdx.x == 0) {
+    mbar_init(k_full, 1);
+    mbar_init(v_full, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&q_full[s], 1);
+      mbar_init(&q_empty[s], 1);
+    }
+    mbar_init(do_full, 1);
+    mbar_init(do_empty, 1);
+    mbar_init(s_full, 1);
+    mbar_init(dp_full, 1);
+    mbar_init(p_full, 256);
+    mbar_init(ds_full, 256);
+    mbar_init(ds_empty, 1);
+    mbar_init(dq_full, 1);
+    mbar_init(dq_empty, 128);
+    mbar_init(dkv_full, 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(tmem_ptr_smem, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  uint8_t* sK = smem + L::kKOff;
+  uint8_t* sV = smem + L::kVOff;
+  uint8_t* sQ = smem + L::kQOff;
+  uint8_t* sDo = smem + L::kDoOff;
+  uint8_t* sDs = smem + L::kDsOff;
+  uint8_t* sDq = smem + L::kDqOff;
+  float* sStat = reinterpret_cast<float*>(smem + L::kStatOff);
+  uint32_t* sMask = reinterpret_cast<uint32_t*>(smem + L::kMaskOff);
+
+  constexpr uint32_t kColS = 0, kColDP = 128, kColDV = 256, kColDK = 384;
+
+  if (warp >= 12) {
+    setmaxnreg_dec<kOtherRegs>();
+    if (warp == 13) {
+      // ===================================== TMA loader ========================================
+      if (elect_one()) {
+        tma_prefetch_desc(&maps.q);
+        tma_prefetch_desc(&maps.k);
+        tma_prefetch_desc(&maps.v);
+        tma_prefetch_desc(&maps.dout);
+        if (n_iter > 0) {   // nobody waits for K / V otherwise, and a CTA must not exit with loads in flight
+          mbar_arrive_expect_tx(k_full, L::kTile);
+#pragma unroll
+          for (int c = 0; c < DPAD / 64; ++c) tma_load_3d(sK + c * L::kSub, &maps.k, k_full, c * 64, bidh, seq.k_begin + k0);
+          mbar_arrive_expect_tx(v_full, L::kTile);
+#pragma unroll
+          for (int c = 0; c < DPAD / 64; ++c) tma_load_3d(sV + c * L::kSub, &maps.v, v_full, c * 64, bidh, seq.k_begin + k0);
+        }
+        for (int it = 0; it < n_iter; ++it) {
+          const int m = tile_of(it);
+          const int s = it & 1;
+          mbar_wait(&q_empty[s], ((it >> 1) & 1) ^ 1);
+          mbar_arrive_expect_tx(&q_full[s], L::kTile + 1024);
+#pragma unroll
+          for (int c = 0; c < DPAD / 64; ++c)
+            tma_load_3d(sQ + s * L::kTile + c * L::kSub, &maps.q, &q_full[s], c * 64, bidh, seq.q_begin + m * kBM);
+          const int64_t stat_off = (int64_t)bh * ws.sq_pad + m * kBM;
+          bulk_load_1d(sStat + s * 256, ws.nl + stat_off, 512, &q_full[s]);
+          bulk_load_1d(sStat + s * 256 + 128, ws.dsum + stat_off, 512, &q_full[s]);
+          mbar_wait(do_empty, (it & 1) ^ 1);
+          mbar_arrive_expect_tx(do_full, L::kTile);
+#pragma unroll
+          for (int c = 0; c < DPAD / 64; ++c)
+            tma_load_3d(sDo + c * L::kSub, &maps.dout, do_full, c * 64, bidh, seq.q_begin + m * kBM);
+        }
+      }
+    } else if (warp == 12) {
+      // ===================================== MMA issuer ========================================
+      if (elect_one() && n_iter > 0) {
+        const uint32_t idesc_st = make_idesc_f16(kBf16, 128, 128, false, false);    // S^T, dP^T
+        const uint32_t idesc_kv = make_idesc_f16(kBf16, 128, DPAD, false, true);    // dV, dK (B = dO / Q, MN-major)
+        const uint32_t idesc_dq = make_idesc_f16(kBf16, 128, DPAD, true, true);     // dQ (A = dS^T read MN-major)
+        const uint32_t aK = smem_u32(sK), aV = smem_u32(sV), aQ = smem_u32(sQ), aDo = smem_u32(sDo), aDs = smem_u32(sDs);
+        const uint32_t tS = tmem_base + kColS, tDP = tmem_base + kColDP, tDV = tmem_base + kColDV, tDK = tmem_base + kColDK;
+
+        // D[keys x queries] = A[keys x d] B[queries x d]^T, both K-major
+        auto issue_t = [&](uint32_t d_tmem, uint32_t a_base, uint32_t b_base) {
+#pragma unroll
+          for (int kk = 0; kk < DPAD / 16; ++kk) {
+            const uint32_t off = (kk >> 2) * L::kSub + (kk & 3) * 32;
+            umma_ss(d_tmem, make_smem_desc_sw128(a_base + off, 16, 1024), make_smem_desc_sw128(b_base + off, 16, 1024),
+                    idesc_st, kk > 0 ? 1u : 0u);
+          }
+        };
+        // dV[keys x d] += P^T[keys x queries] (TMEM, 16 bit) dO[queries x d]
+        auto issue_dv = [&](bool acc) {
+#pragma unroll
+          for (int kk = 0; kk < kBM / 16; ++kk) {
+            const uint32_t a_col = (kk < 4) ? kk * 8 : 64 + (kk - 4) * 8;   // warpgroup 1's half lives at column 64
+            umma_ts(tDV, tS + a_col, make_smem_desc_sw128(aDo + kk * 2048, L::kSub, 1024), idesc_kv,
+                    (acc || kk > 0) ? 1u : 0u);
+          }
+        };
+        // dK[keys x d] += dS^T[keys x queries] (smem, K-major) Q[queries x d] (MN-major)
+        auto issue_dk = [&](uint32_t q_base, bool acc) {
+#pragma unroll
+          for (int kk = 0; kk < kBM / 16; ++kk) {
+            const uint32_t off = (kk >> 2) * L::kSub + (kk & 3) * 32;
+            umma_ss(tDK, make_smem_desc_sw128(aDs + off, 16, 1024), make_smem_desc_sw128(q_base + kk * 2048, L::kSub, 1024),
+                    idesc_kv, (acc || kk > 0) ? 1u : 0u);
+          }
+        };
+        // dQ[queries x d] = dS[queries x keys] (= dS^T tile read MN-major) K[keys x d] (MN-major)
+        auto issue_dq = [&]() {
+#pragma unroll
+          for (int kk = 0; kk < kBN / 16; ++kk) {
+            umma_ss(tDP, make_smem_desc_sw128(aDs + kk * 2048, L::kSub, 1024),
+                    make_smem_desc_sw128(aK + kk * 2048, L::kSub, 1024), idesc_dq, kk > 0 ? 1u : 0u);
+          }
+        };
+
+        mbar_wait(k_full, 0);
+        mbar_wait(&q_full[0], 0);
+        tc_fence_after();
+        issue_t(tS, aK, aQ);
+        umma_commit(s_full);
+        mbar_wait(v_full, 0);
+        mbar_wait(do_full, 0);
+        tc_fence_after();
+        issue_t(tDP, aV, aDo);
+        umma_commit(dp_full);
+        for (int it = 0; it < n_iter; ++it) {
+          const int s = it & 1;
+          const bool has_next = it + 1 < n_iter;
+          mbar_wait(p_full, it & 1);
+          tc_fence_after();
+          issue_dv(it > 0);
+          umma_commit(do_empty);
+          if (has_next) {
+            mbar_wait(&q_full[s ^ 1], ((it + 1) >> 1) & 1);
+            tc_fence_after();
+            issue_t(tS, aK, aQ + (s ^ 1) * L::kTile);
+            umma_commit(s_full);
+          }
+          mbar_wait(ds_full, it & 1);
+          tc_fence_after();
+          issue_dk(aQ + s * L::kTile, it > 0);
+          umma_commit(&q_empty[s]);
+          issue_dq();
+          umma_commit(dq_full);
+          umma_commit(ds_empty);
+          if (has_next) {
+            mbar_wait(dq_empty, it & 1);
+            mbar_wait(do_full, (it + 1) & 1);
+            tc_fence_after();
+            issue_t(tDP, aV, aDo);
+            umma_commit(dp_full);
+          }
+        }
+        umma_commit(dkv_full);
+      }
+    }
+  } else if (warp >= 8) {
+    // ===================================== dQ drain warps ======================================
+    setmaxnreg_dec<kDrainRegs>();
+    const int wq = warp & 3;
+    const int row = wq * 32 + lane;
+    const int rtid = threadIdx.x - 256;
+    const uint32_t tDQ = tmem_base + (static_cast<uint32_t>(wq * 32) << 16) + kColDP;
+    const uint32_t stage0 = smem_u32(sDq);
+    constexpr int kChunks = DPAD / 16;
+    uint32_t n_issued = 0;
+    for (int it = 0; it < n_iter; ++it) {
+      const int m = tile_of(it);
+      float* gtile = ws.dq_accum + ((int64_t)bh * ws.n_qtiles + m) * (kBM * DPAD);
+      mbar_wait(dq_full, it & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int ch = 0; ch < kChunks; ++ch) {
+        const uint32_t buf = n_issued & 1;
+        if (rtid == 0 && n_issued >= 2) bulk_wait_group_read<1>();   // the bulk op that last read this buffer is done
+        named_bar_sync(2, 128);
+        uint32_t v[16];
+        tmem_ld16(tDQ + ch * 16, v);
+        tmem_wait_ld();
+        if (ch == kChunks - 1) {
+          tc_fence_before();
+          mbar_arrive(dq_empty);
+        }
+        const uint32_t dst = stage0 + buf * L::kDqStageBytes + row * 16;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) st_shared_v4(dst + g * 2048, v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
+        fence_proxy_async();
+        named_bar_sync(2, 128);
+        if (rtid == 0) {
+          bulk_reduce_add_f32(gtile + ch * 2048, sDq + buf * L::kDqStageBytes, L::kDqStageBytes);
+          bulk_commit_group();
+        }
+        ++n_issued;
+      }
+    }
+    if (rtid == 0) bulk_wait_group<0>();
+  } else {
+    // ===================================== compute warps =======================================
+    setmaxnreg_inc<kComputeRegs>();
+    const int g = warp >> 2;            // query half of the tile
+    const int wq = warp & 3;            // TMEM lane quarter
+    const int kl = wq * 32 + lane;      // key row within the block (= TMEM lane)
+    const int key = k0 + kl;
+    const bool key_valid = key < seq.seqlen_k;
+    const bool kv_partial = k0 + kBN > seq.seqlen_k;
+    const uint32_t lane_base = static_cast<uint32_t>(wq * 32) << 16;
+    const uint32_t tS = tmem_base + lane_base + kColS + g * 64;
+    const uint32_t tDP = tmem_base + lane_base + kColDP + g * 64;
+    const float scale_log2 = p.softmax_scale * kLog2e;
+    const float rp_dropout = 1.f / (1.f - p.p_dropout);
+    const PhiloxKey pk = make_philox_key(p.philox_seed, p.philox_offset);
+    const uint32_t keep_thr = keep_threshold_u16(p.p_dropout);
+    const uint32_t ds_row = smem_u32(sDs) + g * L::kSub + kl * 128;
+
+    for (int it = 0; it < n_iter; ++it) {
+      const int m = tile_of(it);
+      const int s = it & 1;
+      const float* nl_s = sStat + s * 256 + g * 64;
+      const float* d_s = sStat + s * 256 + 128 + g * 64;
+
+      uint64_t keepbits = ~0ull;
+      if (kDropout) {
+        // all 256 compute threads build the tile's keep bits: word (w, q) = 32 keys k0+32w.. of query row q
+        uint32_t* mbuf = sMask + (it & 1) * 512;
+#pragma unroll
+        for (int rep = 0; rep < 2; ++rep) {
+          const int idx = threadIdx.x + rep * 256;
+          const int ql = idx & 127, w = idx >> 7;
+          uint32_t word = 0;
+#pragma unroll
+          for (int kg = 0; kg < 4; ++kg) {
+            const uint4 r = dropout_rand8(pk, bh, static_cast<uint32_t>(m * kBM + ql), static_cast<uint32_t>((k0 >> 3) + w * 4 + kg));
+            const uint32_t rw[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              word |= ((rw[e] & 0xFFFFu) <= keep_thr ? 1u : 0u) << (kg * 8 + 2 * e);
+              word |= ((rw[e] >> 16) <= keep_thr ? 1u : 0u) << (kg * 8 + 2 * e + 1);
+            }
+          }
+          mbuf[w * 128 + ql] = word;
+        }
+        named_bar_sync(1, 256);
+        const uint32_t* mrow = mbuf + wq * 128 + g * 64;
+        keepbits = 0;
+#pragma unroll
+        for (int c4 = 0; c4 < 16; ++c4) {
+          const uint4 w4 = *reinterpret_cast<const uint4*>(mrow + c4 * 4);
+          keepbits |= static_cast<uint64_t>((w4.x >> lane) & 1u) << (c4 * 4);
+          keepbits |= static_cast<uint64_t>((w4.y >> lane) & 1u) << (c4 * 4 + 1);
+          keepbits |= static_cast<uint64_t>((w4.z >> lane) & 1u) << (c4 * 4 + 2);
+          keepbits |= static_cast<uint64_t>((w4.w >> lane) & 1u) << (c4 * 4 + 3);
+        }
+      }
+
+      // column validity of (this key, query column c): key padding, causal diagonal, blocksparse row groups
+      uint64_t colmask = ~0ull;
+      bool need_mask = kv_partial;
+      if (kv_partial && !key_valid) colmask = 0;
+      if (kCausal && m == n_blk) {
+        need_mask = true;
+        const int first = kl - g * 64;     // query column c is visible iff c >= first
+        colmask &= first <= 0 ? ~0ull : (first >= 64 ? 0ull : (~0ull << first));
+      }
+      if (kSparse) {
+        need_mask = true;
+        const uint32_t f = (static_cast<uint32_t>(tile_flags[m]) >> (g * 4)) & 0xFu;
+        uint64_t e = 0;
+#pragma unroll
+        for (int b4 = 0; b4 < 4; ++b4)
+          if (f & (1u << b4)) e |= 0xFFFFull << (16 * b4);
+        colmask &= e;
+      }
+
+      mbar_wait(&q_full[s], (it >> 1) & 1);   // -lse*log2e and D of this tile are in shared memory
+      mbar_wait(s_full, it & 1);
+      tc_fence_after();
+
+      // ---- P^T = exp2(S^T * scale*log2e - lse*log2e); keep fp32 P for dS, write (P o Z) as 16 bit for dV ----
+      float pf[64];
+#pragma unroll
+      for (int ch = 0; ch < 2; ++ch) {
+        uint32_t r[32];
+        tmem_ld32(tS + ch * 32, r);
+        tmem_wait_ld();
+#pragma unroll
+        for (int c4 = 0; c4 < 8; ++c4) {
+          const float4 nl = *reinterpret_cast<const float4*>(nl_s + ch * 32 + c4 * 4);
+          pf[ch * 32 + c4 * 4 + 0] = ex2(fmaf(__uint_as_float(r[c4 * 4 + 0]), scale_log2, nl.x));
+          pf[ch * 32 + c4 * 4 + 1] = ex2(fmaf(__uint_as_float(r[c4 * 4 + 1]), scale_log2, nl.y));
+          pf[ch * 32 + c4 * 4 + 2] = ex2(fmaf(__uint_as_float(r[c4 * 4 + 2]), scale_log2, nl.z));
+          pf[ch * 32 + c4 * 4 + 3] = ex2(fmaf(__uint_as_float(r[c4 * 4 + 3]), scale_log2, nl.w));
+        }
+        if (need_mask) {
+          const uint32_t mb = static_cast<uint32_t>(colmask >> (ch * 32));
+#pragma unroll
+          for (int c = 0; c < 32; ++c)
+            if (!((mb >> c) & 1u)) pf[ch * 32 + c] = 0.f;
+        }
+        uint32_t pp[16];
+        if (kDropout) {
+          const uint32_t kb = static_cast<uint32_t>(keepbits >> (ch * 32));
+#pragma unroll
+          for (int c2 = 0; c2 < 16; ++c2) {
+            const float lo = ((kb >> (2 * c2)) & 1u) ? pf[ch * 32 + 2 * c2] : 0.f;
+            const float hi = ((kb >> (2 * c2 + 1)) & 1u) ? pf[ch * 32 + 2 * c2 + 1] : 0.f;
+            pp[c2] = pack2<kBf16>(lo, hi);
+          }
+        } else {
+#pragma unroll
+          for (int c2 = 0; c2 < 16; ++c2) pp[c2] = pack2<kBf16>(pf[ch * 32 + 2 * c2], pf[ch * 32 + 2 * c2 + 1]);
+        }
+        tmem_st16(tS + ch * 16, pp);   // P^T of this half: columns [64g, 64g+32), aliasing the S^T columns already read
+      }
+      tmem_wait_st();
+      tc_fence_before();
+      mbar_arrive(p_full);
+
+      // ---- dS^T = P^T o (dP^T o Z / keep - D), 16 bit, into swizzled shared memory ----
+      mbar_wait(dp_full, it & 1);
+      tc_fence_after();
+      if (it > 0) mbar_wait(ds_empty, (it - 1) & 1);   // dK / dQ MMAs of the previous tile have read sDs
+#pragma unroll
+      for (int ch = 0; ch < 2; ++ch) {
+        uint32_t r[32];
+        tmem_ld32(tDP + ch * 32, r);
+        tmem_wait_ld();
+        uint32_t dsp[16];
+        const uint32_t kb = static_cast<uint32_t>(keepbits >> (ch * 32));
+#pragma unroll
+        for (int c4 = 0; c4 < 8; ++c4) {
+          const float4 dd = *reinterpret_cast<const float4*>(d_s + ch * 32 + c4 * 4);
+          const float dsum[4] = {dd.x, dd.y, dd.z, dd.w};
+          float dsv[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int c = c4 * 4 + e;
+            float dp = __uint_as_float(r[c]);
+            if (kDropout) dp = ((kb >> c) & 1u) ? dp * rp_dropout : 0.f;
+            dsv[e] = pf[ch * 32 + c] * (dp - dsum[e]);
+          }
+          dsp[c4 * 2] = pack2<kBf16>(dsv[0], dsv[1]);
+          dsp[c4 * 2 + 1] = pack2<kBf16>(dsv[2], dsv[3]);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t chunk = static_cast<uint32_t>((ch * 4 + j) ^ (kl & 7));
+          st_shared_v4(ds_row + chunk * 16, dsp[4 * j], dsp[4 * j + 1], dsp[4 * j + 2], dsp[4 * j + 3]);
+        }
+      }
+      tc_fence_before();
+      fence_proxy_async();
+      mbar_arrive(ds_full);
+    }
+
+    // ---- epilogue: warpgroup 0 stores dV (x 1/keep), warpgroup 1 stores dK (x scale) ----
+    {
+      using T = typename Elem<kBf16>::T;
+      if (n_iter > 0) {
+        mbar_wait(dkv_full, 0);
+        tc_fence_after();
+      }
+      const uint32_t tAcc = tmem_base + lane_base + (g == 0 ? kColDV : kColDK);
+      const float out_scale = g == 0 ? (kDropout ? rp_dropout : 1.f) : p.softmax_scale;
+      T* orow = g == 0 ? reinterpret_cast<T*>(p.dv) + (int64_t)(seq.k_begin + key) * p.dv_row_stride + (int64_t)bidh * p.dv_head_stride
+                       : reinterpret_cast<T*>(p.dk) + (int64_t)(seq.k_begin + key) * p.dk_row_stride + (int64_t)bidh * p.dk_head_stride;
+#pragma unroll
+      for (int c4 = 0; c4 < DPAD / 32; ++c4) {
+        uint32_t o[32];
+        if (n_iter > 0) {
+          tmem_ld32(tAcc + c4 * 32, o);
+          tmem_wait_ld();
+        } else {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) o[c] = 0u;
+        }
+        if (key_valid) {
+#pragma unroll
+          for (int v8 = 0; v8 < 4; ++v8) {
+            const int col = c4 * 32 + v8 * 8;
+            if (col < p.d) {
+              uint4 pk4;
+              pk4.x = pack2<kBf16>(__uint_as_float(o[v8 * 8 + 0]) * out_scale, __uint_as_float(o[v8 * 8 + 1]) * out_scale);
+              pk4.y = pack2<kBf16>(__uint_as_float(o[v8 * 8 + 2]) * out_scale, __uint_as_float(o[v8 * 8 + 3]) * out_scale);
+              pk4.z = pack2<kBf16>(__uint_as_float(o[v8 * 8 + 4]) * out_scale, __uint_as_float(o[v8 * 8 + 5]) * out_scale);
+              pk4.w = pack2<kBf16>(__uint_as_float(o[v8 * 8 + 6]) * out_scale, __uint_as_float(o[v8 * 8 + 7]) * out_scale);
+              *reinterpret_cast<uint4*>(orow + col) = pk4;
+            }
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// preprocess: D = rowsum(dO o O) -> softmax_d and the padded workspace copy; -lse*log2e -> workspace
+// 16 threads per query row (8 elements = 16 bytes each), 16 rows per CTA.
+// ------------------------------------------------------------------------------------------------
+template <bool kBf16>
+__global__ void __launch_bounds__(256) bwd_preprocess_kernel(const fa_params p, const BwdWs ws) {
+  using T = typename Elem<kBf16>::T;
+  const int bidb = blockIdx.z, bidh = blockIdx.y;
+  const SeqInfo seq(p.cu_seqlens_q, p.cu_seqlens_k, bidb);
+  const int row = blockIdx.x * 16 + (threadIdx.x >> 4);
+  const int part = threadIdx.x & 15;
+  const bool valid = row < seq.seqlen_q;
+  float acc = 0.f;
+  if (valid && part * 8 < p.d) {
+    const int64_t r = seq.q_begin + row;
+    const uint4 ov = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.o) + r * p.o_row_stride + (int64_t)bidh * p.o_head_stride + part * 8));
+    const uint4 gv = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.dout) + r * p.do_row_stride + (int64_t)bidh * p.do_head_stride + part * 8));
+    const T* oe = reinterpret_cast<const T*>(&ov);
+    const T* ge = reinterpret_cast<const T*>(&gv);
+#pragma unroll
+    for (int t = 0; t < 8; ++t) acc = fmaf(Elem<kBf16>::to_float(oe[t]), Elem<kBf16>::to_float(ge[t]), acc);
+  }
+#pragma unroll
+  for (int o = 8; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (part == 0 && row < ws.sq_pad) {
+    const int64_t bh = (int64_t)bidb * p.h + bidh;
+    float nl = -INFINITY;
+    if (valid) {
+      const float lse = p.softmax_lse[bh * p.seqlen_q_rounded + row];
+      if (lse != -INFINITY) nl = -lse * kLog2e;
+    }
+    ws.nl[bh * ws.sq_pad + row] = nl;
+    ws.dsum[bh * ws.sq_pad + row] = valid ? acc : 0.f;
+    if (row < p.seqlen_q_rounded) p.softmax_d[bh * p.seqlen_q_rounded + row] = valid ? acc : 0.f;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// postprocess: dq = scale * dq_accum (tile layout [DPAD/4][128 rows][4]) -> 16 bit, caller's strides
+// ------------------------------------------------------------------------------------------------
+template <bool kBf16, int DPAD>
+__global__ void __launch_bounds__(256) bwd_postprocess_kernel(const fa_params p, const BwdWs ws) {
+  using T = typename Elem<kBf16>::T;
+  const int bidb = blockIdx.z, bidh = blockIdx.y, m = blockIdx.x;
+  const SeqInfo seq(p.cu_seqlens_q, p.cu_seqlens_k, bidb);
+  const int r = threadIdx.x & 127, half = threadIdx.x >> 7;
+  const int row = m * kBM + r;
+  if (row >= seq.seqlen_q) return;
+  const float* tile = ws.dq_accum + (((int64_t)bidb * p.h + bidh) * ws.n_qtiles + m) * (kBM * DPAD);
+  T* out = reinterpret_cast<T*>(p.dq) + (int64_t)(seq.q_begin + row) * p.dq_row_stride + (int64_t)bidh * p.dq_head_stride;
+  const float sc = p.softmax_scale;
+#pragma unroll
+  for (int cg = 0; cg < DPAD / 32; ++cg) {          // 16 columns per step
+    const int col = half * (DPAD / 2) + cg * 16;
+    if (col >= p.d) break;
+    float4 v[4];
+#pragma unroll
+    for (int gq = 0; gq < 4; ++gq) v[gq] = *reinterpret_cast<const float4*>(tile + (col / 4 + gq) * 512 + r * 4);
+    uint4 a, b;
+    a.x = pack2<kBf16>(v[0].x * sc, v[0].y * sc);
+    a.y = pack2<kBf16>(v[0].z * sc, v[0].w * sc);
+    a.z = pack2<kBf16>(v[1].x * sc, v[1].y * sc);
+    a.w = pack2<kBf16>(v[1].z * sc, v[1].w * sc);
+    b.x = pack2<kBf16>(v[2].x * sc, v[2].y * sc);
+    b.y = pack2<kBf16>(v[2].z * sc, v[2].w * sc);
+    b.z = pack2<kBf16>(v[3].x * sc, v[3].y * sc);
+    b.w = pack2<kBf16>(v[3].z * sc, v[3].w * sc);
+    *reinterpret_cast<uint4*>(out + col) = a;
+    if (col + 8 < p.d) *reinterpret_cast<uint4*>(out + col + 8) = b;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+inline uint64_t align256(uint64_t x) { return (x + 255) & ~uint64_t(255); }
+
+struct BwdWsLayout {
+  uint64_t nl_off, dsum_off, accum_off, total;
+  int sq_pad, n_qtiles, dpad;
+};
+
+BwdWsLayout bwd_ws_layout(const fa_params& p) {
+  BwdWsLayout l;
+  l.n_qtiles = (p.max_seqlen_q + kBM - 1) / kBM;
+  l.sq_pad = l.n_qtiles * kBM;
+  l.dpad = p.d <= 64 ? 64 : 128;
+  const uint64_t rows = (uint64_t)p.b * p.h * l.sq_pad;
+  l.nl_off = 0;
+  l.dsum_off = align256(rows * 4);
+  l.accum_off = l.dsum_off + align256(rows * 4);
+  l.total = l.accum_off + align256(rows * l.dpad * 4);
+  return l;
+}
+
+template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse>
+cudaError_t launch_bwd_variant(const BwdTensorMaps& maps, const fa_params& p, const BlockMaskView& bm, const BwdWs& ws,
+                               cudaStream_t stream) {
+  auto kernel = bwd_sm100_kernel<DPAD, kBf16, kCausal, kDropout, kSparse>;
+  constexpr int smem = BwdSmem<DPAD>::kDynamicBytes;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return e;
+  const dim3 grid((p.max_seqlen_k + kBN - 1) / kBN, p.h, p.b);
+  kernel<<<grid, kBwdThreads, smem, stream>>>(maps, p, bm, ws);
+  count_launch();
+  return cudaGetLastError();
+}
+
+template <int DPAD, bool kBf16>
+cudaError_t dispatch_bwd_flags(const BwdTensorMaps& maps, const fa_params& p, const BlockMaskView& bm, const BwdWs& ws,
+                               cudaStream_t stream) {
+  const bool drop = p.p_dropout > 0.f;
+  if (bm.dense != nullptr) {
+    return drop ? launch_bwd_variant<DPAD, kBf16, false, true, true>(maps, p, bm, ws, stream)
+                : launch_bwd_variant<DPAD, kBf16, false, false, true>(maps, p, bm, ws, stream);
+  }
+  if (p.is_causal) {
+    return drop ? launch_bwd_variant<DPAD, kBf16, true, true, false>(maps, p, bm, ws, stream)
+                : launch_bwd_variant<DPAD, kBf16, true, false, false>(maps, p, bm, ws, stream);
+  }
+  return drop ? launch_bwd_variant<DPAD, kBf16, false, true, false>(maps, p, bm, ws, stream)
+              : launch_bwd_variant<DPAD, kBf16, false, false, false>(maps, p, bm, ws, stream);
+}
+
+}  // namespace
+
+uint64_t bwd_sm100_workspace_bytes(const fa_params& p) { return bwd_ws_layout(p).total; }
+
+cudaError_t launch_bwd_sm100(const fa_params& p, const BlockMaskView& bm, void* workspace, cudaStream_t stream,
+                             const char** err_msg) {
   *err_msg = nullptr;
-  return launch_simt_bwd(p, bm, stream);
+  const BwdWsLayout l = bwd_ws_layout(p);
+  if (bm.dense != nullptr && l.n_qtiles > kMaxSparseTiles) {
+    *err_msg = "blocksparse backward supports at most 65536 queries per sequence";
+    return cudaErrorInvalidValue;
+  }
+  uint8_t* base = static_cast<uint8_t*>(workspace);
+  BwdWs ws;
+  ws.nl = reinterpret_cast<float*>(base + l.nl_off);
+  ws.dsum = reinterpret_cast<float*>(base + l.dsum_off);
+  ws.dq_accum = reinterpret_cast<float*>(base + l.accum_off);
+  ws.sq_pad = l.sq_pad;
+  ws.n_qtiles = l.n_qtiles;
+  cudaError_t e;
+  if (l.n_qtiles > 0) {
+    e = cudaMemsetAsync(ws.dq_accum, 0, (uint64_t)p.b * p.h * l.sq_pad * l.dpad * 4, stream);
+    if (e != cudaSuccess) return e;
+    const dim3 grid(l.sq_pad / 16, p.h, p.b);
+    if (p.is_bf16) bwd_preprocess_kernel<true><<<grid, 256, 0, stream>>>(p, ws);
+    else bwd_preprocess_kernel<false><<<grid, 256, 0, stream>>>(p, ws);
+    count_launch();
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+  }
+  if (p.max_seqlen_k > 0 && p.total_k > 0) {
+    BwdTensorMaps maps;
+    const int64_t tq = p.total_q > 0 ? p.total_q : 1;
+    const void* qptr = p.total_q > 0 ? p.q : p.k;         // never dereferenced when there are no query rows
+    const void* doptr = p.total_q > 0 ? p.dout : p.k;
+    if (!make_tensor_map_3d(&maps.q, qptr, p.d, p.h, tq, p.q_row_stride, p.q_head_stride, kBM) ||
+        !make_tensor_map_3d(&maps.k, p.k, p.d, p.h, p.total_k, p.k_row_stride, p.k_head_stride, kBN) ||
+        !make_tensor_map_3d(&maps.v, p.v, p.d, p.h, p.total_k, p.v_row_stride, p.v_head_stride, kBN) ||
+        !make_tensor_map_3d(&maps.dout, doptr, p.d, p.h, tq, p.do_row_stride, p.do_head_stride, kBM)) {
+      *err_msg = "cuTensorMapEncodeTiled failed (q/k/v/dout must be 16-byte aligned with 16-byte-multiple strides)";
+      return cudaErrorInvalidValue;
+    }
+    if (p.d <= 64) e = p.is_bf16 ? dispatch_bwd_flags<64, true>(maps, p, bm, ws, stream) : dispatch_bwd_flags<64, false>(maps, p, bm, ws, stream);
+    else e = p.is_bf16 ? dispatch_bwd_flags<128, true>(maps, p, bm, ws, stream) : dispatch_bwd_flags<128, false>(maps, p, bm, ws, stream);
+    if (e != cudaSuccess) return e;
+  }
+  if (l.n_qtiles > 0 && p.total_q > 0) {
+    const dim3 grid(l.n_qtiles, p.h, p.b);
+    if (l.dpad == 64) {
+      if (p.is_bf16) bwd_postprocess_kernel<true, 64><<<grid, 256, 0, stream>>>(p, ws);
+      else bwd_postprocess_kernel<false, 64><<<grid, 256, 0, stream>>>(p, ws);
+    } else {
+      if (p.is_bf16) bwd_postprocess_kernel<true, 128><<<grid, 256, 0, stream>>>(p, ws);
+      else bwd_postprocess_kernel<false, 128><<<grid, 256, 0, stream>>>(p, ws);
+    }
+    count_launch();
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
 }
 
 }  // namespace fa

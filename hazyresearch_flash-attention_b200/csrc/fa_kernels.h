@@ -1,5 +1,6 @@
 // Internal launcher declarations shared by the translation units of libfa_b200.so.
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 
 #include "fa_common.cuh"
@@ -17,7 +18,12 @@ cudaError_t launch_dot_do_o(const fa_params& p, cudaStream_t stream);
 // --- tcgen05 / TMA kernels (fa_fwd_sm100.cu, fa_bwd_sm100.cu) ---
 // Return cudaSuccess or the failing CUDA error; *err_msg (static string) describes non-CUDA failures.
 cudaError_t launch_fwd_sm100(const fa_params& p, const BlockMaskView& bm, cudaStream_t stream, const char** err_msg);
-cudaError_t launch_bwd_sm100(const fa_params& p, const BlockMaskView& bm, cudaStream_t stream, const char** err_msg);
+// `workspace` points at bwd_sm100_workspace_bytes(p) bytes of scratch (256-byte aligned).
+cudaError_t launch_bwd_sm100(const fa_params& p, const BlockMaskView& bm, void* workspace, cudaStream_t stream,
+                             const char** err_msg);
+// (d, h, total) TMA view of a packed (total, h, d) 16-bit tensor: box 64 x 1 x box_rows, 128-byte swizzle (fa_fwd_sm100.cu)
+bool make_tensor_map_3d(CUtensorMap* map, const void* base, int d, int h, int64_t total, int64_t row_stride,
+                        int64_t head_stride, int box_rows);
 uint64_t bwd_sm100_workspace_bytes(const fa_params& p);
 
 // --- small utility kernels (fa_api.cu) ---

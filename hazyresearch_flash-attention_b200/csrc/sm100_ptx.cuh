@@ -83,6 +83,26 @@ FA_DEVICE void tma_load_3d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, 
       : "memory");
 }
 
+// 1-D bulk copy global -> shared, completion on an mbarrier (size multiple of 16, 16-byte aligned both sides)
+FA_DEVICE void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(gsrc)), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+// 1-D bulk reduction shared -> global: gdst[i] += ssrc[i] (fp32), tracked by the thread's bulk async-group
+FA_DEVICE void bulk_reduce_add_f32(void* gdst, const void* smem_src, uint32_t bytes) {
+  asm volatile(
+      "cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;\n"
+      ::"l"(reinterpret_cast<uint64_t>(gdst)), "r"(smem_u32(smem_src)), "r"(bytes)
+      : "memory");
+}
+FA_DEVICE void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;\n" ::: "memory"); }
+template <int N>
+FA_DEVICE void bulk_wait_group_read() { asm volatile("cp.async.bulk.wait_group.read %0;\n" ::"n"(N) : "memory"); }
+template <int N>
+FA_DEVICE void bulk_wait_group() { asm volatile("cp.async.bulk.wait_group %0;\n" ::"n"(N) : "memory"); }
+
 // ------------------------------------------------------------------------------------------------
 // tcgen05: TMEM allocation
 // ------------------------------------------------------------------------------------------------

