@@ -7,6 +7,8 @@
 #include <cstdio>
 #include <cstring>
 #include <atomic>
+#include <mutex>
+#include <vector>
 
 #include "fa_common.cuh"
 #include "fa_kernels.h"
@@ -242,6 +244,31 @@ int run_bwd(const fa_params* p, void* stream, bool block) {
 
 }  // namespace
 
+// ---- optional per-kernel device timing (benchmarks): cudaEvents recorded on the launching stream around the
+// main forward / backward kernels while enabled; fa_timing_collect() sums and releases them. ----
+struct TimedSpan { cudaEvent_t a, b; int kind; };
+static std::mutex g_timing_mu;
+static std::vector<TimedSpan> g_spans;
+static std::atomic<int> g_timing_enabled{0};
+bool timing_enabled() { return g_timing_enabled.load(std::memory_order_relaxed) != 0; }
+void* timing_begin(cudaStream_t st) {
+  if (!timing_enabled()) return nullptr;
+  TimedSpan* sp = new TimedSpan;
+  cudaEventCreate(&sp->a);
+  cudaEventCreate(&sp->b);
+  cudaEventRecord(sp->a, st);
+  return sp;
+}
+void timing_end(void* h, int kind, cudaStream_t st) {
+  if (h == nullptr) return;
+  TimedSpan* sp = static_cast<TimedSpan*>(h);
+  sp->kind = kind;
+  cudaEventRecord(sp->b, st);
+  std::lock_guard<std::mutex> lk(g_timing_mu);
+  g_spans.push_back(*sp);
+  delete sp;
+}
+
 static std::atomic<unsigned long long> g_launches{0};
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 unsigned long long launches_so_far() { return g_launches.load(std::memory_order_relaxed); }
@@ -277,6 +304,29 @@ uint64_t fa_workspace_bytes(const fa_params* p, int op) {
 // The dropout stream is keyed by position, so one call consumes one "slot" of the generator; the increment is
 // kept a multiple of 4 like ATen's philox_cuda_state (fmha_api.cpp:228-234).
 uint64_t fa_philox_increment(const fa_params* p) { return (p != nullptr && p->p_dropout > 0.f) ? 4 : 0; }
+
+void fa_timing_enable(int on) { fa::g_timing_enabled.store(on ? 1 : 0); }
+int fa_timing_collect(double* fwd_ms, uint64_t* fwd_launches, double* bwd_ms, uint64_t* bwd_launches) {
+  std::lock_guard<std::mutex> lk(fa::g_timing_mu);
+  double ms[2] = {0.0, 0.0};
+  uint64_t n[2] = {0, 0};
+  int rc = FA_OK;
+  for (auto& sp : fa::g_spans) {
+    float t = 0.f;
+    cudaError_t e = cudaEventSynchronize(sp.b);
+    if (e == cudaSuccess) e = cudaEventElapsedTime(&t, sp.a, sp.b);
+    if (e != cudaSuccess) rc = fa::cuda_fail(e, "fa_timing_collect");
+    else { ms[sp.kind & 1] += t; n[sp.kind & 1] += 1; }
+    cudaEventDestroy(sp.a);
+    cudaEventDestroy(sp.b);
+  }
+  fa::g_spans.clear();
+  if (fwd_ms) *fwd_ms = ms[0];
+  if (fwd_launches) *fwd_launches = n[0];
+  if (bwd_ms) *bwd_ms = ms[1];
+  if (bwd_launches) *bwd_launches = n[1];
+  return rc;
+}
 
 int fa_fwd(const fa_params* p, void* stream) { return fa::run_fwd(p, stream, false); }
 int fa_bwd(const fa_params* p, void* stream) { return fa::run_bwd(p, stream, false); }

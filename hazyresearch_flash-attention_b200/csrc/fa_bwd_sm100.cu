@@ -652,7 +652,9 @@ cudaError_t launch_bwd_variant(const BwdTensorMaps& maps, const fa_params& p, co
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
   const dim3 grid((p.max_seqlen_k + kBN - 1) / kBN, p.h, p.b);
+  void* span = timing_begin(stream);
   kernel<<<grid, kBwdThreads, smem, stream>>>(maps, p, bm, ws);
+  timing_end(span, 1, stream);
   count_launch();
   return cudaGetLastError();
 }

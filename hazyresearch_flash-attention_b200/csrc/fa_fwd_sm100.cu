@@ -469,7 +469,9 @@ cudaError_t launch_fwd_variant(const FwdTensorMaps& maps, const fa_params& p, co
     if (e != cudaSuccess) return e;
   }
   const dim3 grid((p.max_seqlen_q + kBlockM * kTilesPerCta - 1) / (kBlockM * kTilesPerCta), p.h, p.b);
+  void* span = timing_begin(stream);
   kernel<<<grid, kNumThreads, smem, stream>>>(maps, p, bm);
+  timing_end(span, 0, stream);
   count_launch();
   return cudaGetLastError();
 }

@@ -10,6 +10,10 @@ namespace fa {
 // every kernel launch of the library bumps this (fa_launch_count() in the C ABI)
 void count_launch();
 
+// optional device timing of the main kernels (see fa_timing_enable in the C ABI); kind 0 = forward, 1 = backward
+void* timing_begin(cudaStream_t st);
+void timing_end(void* handle, int kind, cudaStream_t st);
+
 // --- CUDA-core cross-check kernels (fa_simt.cu) ---
 cudaError_t launch_simt_fwd(const fa_params& p, const BlockMaskView& bm, bool only_sdmask, cudaStream_t stream);
 cudaError_t launch_simt_bwd(const fa_params& p, const BlockMaskView& bm, cudaStream_t stream);

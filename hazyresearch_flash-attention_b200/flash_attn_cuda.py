@@ -77,6 +77,11 @@ def _load_library():
         raise ImportError(f"{_LIB_PATH}: ABI version {lib.fa_abi_version()} != 1")
     lib.fa_sizeof_params.restype = ctypes.c_uint64
     lib.fa_launch_count.restype = ctypes.c_uint64
+    lib.fa_timing_enable.restype = None
+    lib.fa_timing_enable.argtypes = [ctypes.c_int]
+    lib.fa_timing_collect.restype = ctypes.c_int
+    lib.fa_timing_collect.argtypes = [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_uint64),
+                                      ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_uint64)]
     if lib.fa_sizeof_params() != ctypes.sizeof(FaParams):
         raise ImportError(f"{_LIB_PATH}: sizeof(fa_params) = {lib.fa_sizeof_params()} but the ctypes mirror has "
                           f"{ctypes.sizeof(FaParams)} bytes")
@@ -330,6 +335,20 @@ def scatter_rows(src2d, indices, first_axis_dim):
                                   torch.cuda.current_stream().cuda_stream)
     _raise_if_failed(rc, "fa_scatter_rows")
     return out
+
+
+def kernel_timing(enable):
+    """Benchmarks: bracket the main fwd / bwd kernels with CUDA events on the launching stream."""
+    _lib.fa_timing_enable(1 if enable else 0)
+
+
+def kernel_timing_collect():
+    """-> {'fwd_ms', 'fwd_launches', 'bwd_ms', 'bwd_launches'} summed since the last collect (synchronises)."""
+    f, b = ctypes.c_double(), ctypes.c_double()
+    nf, nb = ctypes.c_uint64(), ctypes.c_uint64()
+    _raise_if_failed(_lib.fa_timing_collect(ctypes.byref(f), ctypes.byref(nf), ctypes.byref(b), ctypes.byref(nb)),
+                     "fa_timing_collect")
+    return {"fwd_ms": f.value, "fwd_launches": nf.value, "bwd_ms": b.value, "bwd_launches": nb.value}
 
 
 def dropout_keep8_host(seed, offset, bh, qrow, kgroup, p_dropout):

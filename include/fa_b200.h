@@ -104,6 +104,12 @@ const char* fa_last_error(void);
 /* number of CUDA kernels this library has launched in this process (monotonic; for benchmarks' launch accounting) */
 uint64_t fa_launch_count(void);
 
+/* Benchmark support: while enabled, the library brackets its main forward / backward kernels with cudaEvents on the
+ * launching stream; fa_timing_collect() waits for them, returns the summed device time (ms) and launch counts since
+ * the last collect, and releases the events.  Off by default (no events are created). */
+void fa_timing_enable(int on);
+int fa_timing_collect(double* fwd_ms, uint64_t* fwd_launches, double* bwd_ms, uint64_t* bwd_launches);
+
 /* bytes of scratch `op` needs for these sizes (0 if none). Pure host arithmetic. */
 uint64_t fa_workspace_bytes(const fa_params* p, int op);
 /* how far the caller must advance its Philox offset after a call with dropout (fmha_api.cpp:228-234). */

@@ -1,0 +1,133 @@
+// Micro-benchmark: issue rate of tcgen05.mma (kind::f16, M=128) for the operand forms the attention kernels use.
+//   nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -I../hazyresearch_flash-attention_b200/csrc mma_bench.cu -o mma_bench
+// Prints cycles per 128 x N x 16 MMA instruction for each variant, with and without concurrent shared-memory stores.
+#include <cstdio>
+#include <cuda_runtime.h>
+#include "sm100_ptx.cuh"
+
+using namespace fa;
+
+constexpr int kSub = 16384;
+
+// variant: 0 SS K/K   1 SS K/MN   2 SS MN/MN   3 TS ./MN   4 TS ./K   5 SS K/K N=256   6 bwd mix (S,dP,dV,dK,dQ)  7 SS K/K N=64
+__global__ void __launch_bounds__(256, 1) mma_bench_kernel(int variant, int reps, int traffic_warps, long long* out) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ uint64_t bar;
+  __shared__ uint32_t tmem_ptr;
+  __shared__ int stop_flag;
+  const int warp = threadIdx.x >> 5;
+  // zero operands (4 tiles of 32 KB)
+  for (int i = threadIdx.x; i < 4 * 32768 / 16; i += blockDim.x) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+  if (threadIdx.x == 0) {
+    mbar_init(&bar, 1);
+    fence_mbar_init();
+    stop_flag = 0;
+  }
+  if (warp == 0) {
+    tmem_alloc(&tmem_ptr, 512);
+    tmem_relinquish();
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tm = tmem_ptr;
+  const uint32_t a0 = smem_u32(smem), b0 = a0 + 32768, c0 = a0 + 65536, d0 = a0 + 98304;
+  if (warp == 0) {
+    if (elect_one()) {
+      const uint32_t id_kk = make_idesc_f16(true, 128, 128, false, false);
+      const uint32_t id_kmn = make_idesc_f16(true, 128, 128, false, true);
+      const uint32_t id_mnmn = make_idesc_f16(true, 128, 128, true, true);
+      const uint32_t id_kk256 = make_idesc_f16(true, 128, 256, false, false);
+      const uint32_t id_kk64 = make_idesc_f16(true, 128, 64, false, false);
+      auto ss_kk = [&](uint32_t d, uint32_t a, uint32_t b, uint32_t id) {
+        for (int kk = 0; kk < 8; ++kk) {
+          const uint32_t off = (kk >> 2) * kSub + (kk & 3) * 32;
+          umma_ss(d, make_smem_desc_sw128(a + off, 16, 1024), make_smem_desc_sw128(b + off, 16, 1024), id, 1);
+        }
+      };
+      auto ss_kmn = [&](uint32_t d, uint32_t a, uint32_t b) {
+        for (int kk = 0; kk < 8; ++kk) {
+          const uint32_t off = (kk >> 2) * kSub + (kk & 3) * 32;
+          umma_ss(d, make_smem_desc_sw128(a + off, 16, 1024), make_smem_desc_sw128(b + kk * 2048, kSub, 1024), id_kmn, 1);
+        }
+      };
+      auto ss_mnmn = [&](uint32_t d, uint32_t a, uint32_t b) {
+        for (int kk = 0; kk < 8; ++kk)
+          umma_ss(d, make_smem_desc_sw128(a + kk * 2048, kSub, 1024), make_smem_desc_sw128(b + kk * 2048, kSub, 1024), id_mnmn, 1);
+      };
+      auto ts_mn = [&](uint32_t d, uint32_t a, uint32_t b) {
+        for (int kk = 0; kk < 8; ++kk) umma_ts(d, a + kk * 8, make_smem_desc_sw128(b + kk * 2048, kSub, 1024), id_kmn, 1);
+      };
+      auto ts_k = [&](uint32_t d, uint32_t a, uint32_t b) {
+        for (int kk = 0; kk < 8; ++kk) {
+          const uint32_t off = (kk >> 2) * kSub + (kk & 3) * 32;
+          umma_ts(d, a + kk * 8, make_smem_desc_sw128(b + off, 16, 1024), id_kk, 1);
+        }
+      };
+      const long long t0 = clock64();
+      for (int r = 0; r < reps; ++r) {
+        switch (variant) {
+          case 0: ss_kk(tm, a0, b0, id_kk); break;
+          case 1: ss_kmn(tm, a0, b0); break;
+          case 2: ss_mnmn(tm, a0, b0); break;
+          case 3: ts_mn(tm, tm + 256, b0); break;
+          case 4: ts_k(tm, tm + 256, b0); break;
+          case 5: ss_kk(tm, a0, b0, id_kk256); break;   // B tile = 2 x 128 rows: b0 and c0 halves are contiguous enough for timing
+          case 6:
+            ss_kk(tm, a0, b0, id_kk);          // S^T
+            ss_kk(tm + 128, c0, d0, id_kk);    // dP^T
+            ts_mn(tm + 256, tm, d0);           // dV
+            ss_kmn(tm + 384, a0, b0);          // dK
+            ss_mnmn(tm + 128, a0, c0);         // dQ
+            break;
+          case 7: ss_kk(tm, a0, b0, id_kk64); break;
+        }
+      }
+      umma_commit(&bar);
+      mbar_wait(&bar, 0);
+      const long long t1 = clock64();
+      if (blockIdx.x == 0) out[0] = t1 - t0;
+      stop_flag = 1;
+      __threadfence_block();
+    }
+  } else if (warp <= traffic_warps) {
+    // concurrent shared-memory store traffic (16 B per lane per store, conflict free) in a scratch region after the operands
+    const uint32_t dst = a0 + 131072 + (threadIdx.x & 1023) * 16;
+    volatile int* sf = &stop_flag;
+    while (*sf == 0) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};\n" ::"r"(dst), "r"(i) : "memory");
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tm, 512);
+  }
+}
+
+int main() {
+  long long* out;
+  cudaMalloc(&out, 8);
+  const int smem = 4 * 32768 + 16384 + 1024;
+  cudaFuncSetAttribute(mma_bench_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  const char* names[] = {"SS K/K N128", "SS K/MN N128", "SS MN/MN N128", "TS ./MN N128", "TS ./K N128", "SS K/K N256", "bwd mix (5 tiles)", "SS K/K N64"};
+  const int reps = 200;
+  for (int traffic = 0; traffic <= 4; traffic += 2) {
+    for (int v = 0; v < 8; ++v) {
+      mma_bench_kernel<<<148, 256, smem>>>(v, reps, traffic, out);
+      cudaError_t e = cudaDeviceSynchronize();
+      if (e != cudaSuccess) { printf("variant %d failed: %s\n", v, cudaGetErrorString(e)); return 1; }
+      long long cyc;
+      cudaMemcpy(&cyc, out, 8, cudaMemcpyDeviceToHost);
+      const int n_instr = reps * 8 * (v == 6 ? 5 : 1);
+      printf("traffic_warps=%d  %-18s  %8.1f clk / MMA instr  (%.0f clk per 128x128x128 tile)\n", traffic, names[v],
+             (double)cyc / n_instr, (double)cyc / n_instr * 8);
+    }
+  }
+  return 0;
+}
