@@ -31,8 +31,8 @@ constexpr int kBM = 128;            // queries per tile
 constexpr int kBN = 128;            // keys per CTA
 constexpr int kBwdThreads = 512;
 constexpr int kComputeRegs = 176;
-constexpr int kDrainRegs = 96;
-constexpr int kOtherRegs = 64;
+constexpr int kDrainRegs = 104;
+constexpr int kOtherRegs = 56;
 constexpr int kMaxSparseTiles = 512;
 
 template <int DPAD>
@@ -64,10 +64,15 @@ struct BwdTensorMaps {
 struct BwdWs {
   float* nl;         // (b*h, sq_pad): -lse*log2e, -inf for rows that must produce P = 0
   float* dsum;       // (b*h, sq_pad): D = rowsum(dO o O), 0 for invalid rows
-  float* dq_accum;   // (b*h, n_qtiles, DPAD/4, 128, 4) fp32
+  float* dq_accum;   // (b*h, n_qtiles, 4 row quarters, DPAD/4, 32, 4) fp32
   int sq_pad, n_qtiles;
 };
 
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];\n" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+  return v;
+}
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
@@ -273,32 +278,43 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
         tc_fence_after();
         issue_t(tDP, aV, aDo);
         umma_commit(dp_full);
+        // software pipeline: slot `it` issues  dQ(it), dK(it) | dV(it+1) | dP(it+1) | S(it+2).  dQ aliases the dP^T
+        // columns, so dP(it+1) has to wait for the drain of dQ(it); dV(it+1) and dK(it) fill that gap.
+        mbar_wait(p_full, 0);
+        tc_fence_after();
+        issue_dv(false);
+        umma_commit(do_empty);
+        if (n_iter > 1) {
+          mbar_wait(&q_full[1], 0);
+          tc_fence_after();
+          issue_t(tS, aK, aQ + L::kTile);
+          umma_commit(s_full);
+        }
         for (int it = 0; it < n_iter; ++it) {
           const int s = it & 1;
-          const bool has_next = it + 1 < n_iter;
-          mbar_wait(p_full, it & 1);
-          tc_fence_after();
-          issue_dv(it > 0);
-          umma_commit(do_empty);
-          if (has_next) {
-            mbar_wait(&q_full[s ^ 1], ((it + 1) >> 1) & 1);
-            tc_fence_after();
-            issue_t(tS, aK, aQ + (s ^ 1) * L::kTile);
-            umma_commit(s_full);
-          }
           mbar_wait(ds_full, it & 1);
           tc_fence_after();
-          issue_dk(aQ + s * L::kTile, it > 0);
-          umma_commit(&q_empty[s]);
           issue_dq();
           umma_commit(dq_full);
+          issue_dk(aQ + s * L::kTile, it > 0);
+          umma_commit(&q_empty[s]);
           umma_commit(ds_empty);
-          if (has_next) {
-            mbar_wait(dq_empty, it & 1);
+          if (it + 1 < n_iter) {
             mbar_wait(do_full, (it + 1) & 1);
+            mbar_wait(p_full, (it + 1) & 1);
+            tc_fence_after();
+            issue_dv(true);
+            mbar_wait(dq_empty, it & 1);
             tc_fence_after();
             issue_t(tDP, aV, aDo);
             umma_commit(dp_full);
+            umma_commit(do_empty);
+            if (it + 2 < n_iter) {
+              mbar_wait(&q_full[s], ((it + 2) >> 1) & 1);
+              tc_fence_after();
+              issue_t(tS, aK, aQ + s * L::kTile);
+              umma_commit(s_full);
+            }
           }
         }
         umma_commit(dkv_full);
@@ -306,44 +322,59 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     }
   } else if (warp >= 8) {
     // ===================================== dQ drain warps ======================================
+    // Each warp drains its own 32 query rows: TMEM -> registers (up to kRing 16-column chunks in flight, so the
+    // TMEM columns are handed back to the MMA warp long before the last chunk reaches global memory) -> a private
+    // 2 x 2 KB staging ring -> one 2 KB cp.reduce.async.bulk per chunk.  No CTA-wide barrier is involved.
     setmaxnreg_dec<kDrainRegs>();
     const int wq = warp & 3;
-    const int row = wq * 32 + lane;
-    const int rtid = threadIdx.x - 256;
     const uint32_t tDQ = tmem_base + (static_cast<uint32_t>(wq * 32) << 16) + kColDP;
-    const uint32_t stage0 = smem_u32(sDq);
+    uint8_t* stage_gen = sDq + wq * 4096;
+    const uint32_t stage = smem_u32(stage_gen);
     constexpr int kChunks = DPAD / 16;
-    uint32_t n_issued = 0;
+    constexpr int kRing = kChunks < 4 ? kChunks : 4;
+    bool primed = false;
     for (int it = 0; it < n_iter; ++it) {
       const int m = tile_of(it);
-      float* gtile = ws.dq_accum + ((int64_t)bh * ws.n_qtiles + m) * (kBM * DPAD);
+      float* gdst = ws.dq_accum + ((int64_t)bh * ws.n_qtiles + m) * (kBM * DPAD) + wq * (32 * DPAD);
       mbar_wait(dq_full, it & 1);
       tc_fence_after();
-#pragma unroll 1
-      for (int ch = 0; ch < kChunks; ++ch) {
-        const uint32_t buf = n_issued & 1;
-        if (rtid == 0 && n_issued >= 2) bulk_wait_group_read<1>();   // the bulk op that last read this buffer is done
-        named_bar_sync(2, 128);
-        uint32_t v[16];
-        tmem_ld16(tDQ + ch * 16, v);
-        tmem_wait_ld();
-        if (ch == kChunks - 1) {
-          tc_fence_before();
-          mbar_arrive(dq_empty);
-        }
-        const uint32_t dst = stage0 + buf * L::kDqStageBytes + row * 16;
+      uint32_t v[kRing][16];
 #pragma unroll
-        for (int g = 0; g < 4; ++g) st_shared_v4(dst + g * 2048, v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
+      for (int c = 0; c < kRing; ++c) tmem_ld16(tDQ + c * 16, v[c]);
+      tmem_wait_ld();
+      if (kRing == kChunks) {
+        tc_fence_before();
+        mbar_arrive(dq_empty);
+      }
+#pragma unroll
+      for (int k = 0; k < kChunks; ++k) {
+        const uint32_t buf = k & 1;
+        if (primed || k >= 2) {
+          if (lane == 0) bulk_wait_group_read<1>();   // the bulk op that last read this buffer is done with it
+          __syncwarp();
+        }
+        const uint32_t dst = stage + buf * 2048 + lane * 16;
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+          st_shared_v4(dst + g * 512, v[k % kRing][4 * g], v[k % kRing][4 * g + 1], v[k % kRing][4 * g + 2], v[k % kRing][4 * g + 3]);
         fence_proxy_async();
-        named_bar_sync(2, 128);
-        if (rtid == 0) {
-          bulk_reduce_add_f32(gtile + ch * 2048, sDq + buf * L::kDqStageBytes, L::kDqStageBytes);
+        __syncwarp();
+        if (lane == 0) {
+          bulk_reduce_add_f32(gdst + k * 512, stage_gen + buf * 2048, 2048);
           bulk_commit_group();
         }
-        ++n_issued;
+        if (k + kRing < kChunks) {
+          tmem_ld16(tDQ + (k + kRing) * 16, v[k % kRing]);
+          tmem_wait_ld();
+          if (k + kRing == kChunks - 1) {
+            tc_fence_before();
+            mbar_arrive(dq_empty);
+          }
+        }
       }
+      primed = true;
     }
-    if (rtid == 0) bulk_wait_group<0>();
+    if (lane == 0) bulk_wait_group<0>();
   } else {
     // ===================================== compute warps =======================================
     setmaxnreg_inc<kComputeRegs>();
@@ -365,8 +396,8 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     for (int it = 0; it < n_iter; ++it) {
       const int m = tile_of(it);
       const int s = it & 1;
-      const float* nl_s = sStat + s * 256 + g * 64;
-      const float* d_s = sStat + s * 256 + 128 + g * 64;
+      const uint32_t nl_s = smem_u32(sStat + s * 256 + g * 64);
+      const uint32_t d_s = smem_u32(sStat + s * 256 + 128 + g * 64);
 
       uint64_t keepbits = ~0ull;
       if (kDropout) {
@@ -427,18 +458,21 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
 
       // ---- P^T = exp2(S^T * scale*log2e - lse*log2e); keep fp32 P for dS, write (P o Z) as 16 bit for dV ----
       float pf[64];
+      {
+        uint32_t(&r)[2][32] = *reinterpret_cast<uint32_t(*)[2][32]>(pf);
+        tmem_ld32(tS, r[0]);
+        tmem_ld32(tS + 32, r[1]);
+        tmem_wait_ld();
+      }
 #pragma unroll
       for (int ch = 0; ch < 2; ++ch) {
-        uint32_t r[32];
-        tmem_ld32(tS + ch * 32, r);
-        tmem_wait_ld();
 #pragma unroll
         for (int c4 = 0; c4 < 8; ++c4) {
-          const float4 nl = *reinterpret_cast<const float4*>(nl_s + ch * 32 + c4 * 4);
-          pf[ch * 32 + c4 * 4 + 0] = ex2(fmaf(__uint_as_float(r[c4 * 4 + 0]), scale_log2, nl.x));
-          pf[ch * 32 + c4 * 4 + 1] = ex2(fmaf(__uint_as_float(r[c4 * 4 + 1]), scale_log2, nl.y));
-          pf[ch * 32 + c4 * 4 + 2] = ex2(fmaf(__uint_as_float(r[c4 * 4 + 2]), scale_log2, nl.z));
-          pf[ch * 32 + c4 * 4 + 3] = ex2(fmaf(__uint_as_float(r[c4 * 4 + 3]), scale_log2, nl.w));
+          const float4 nl = lds128(nl_s + (ch * 32 + c4 * 4) * 4);
+          pf[ch * 32 + c4 * 4 + 0] = ex2(fmaf(pf[ch * 32 + c4 * 4 + 0], scale_log2, nl.x));
+          pf[ch * 32 + c4 * 4 + 1] = ex2(fmaf(pf[ch * 32 + c4 * 4 + 1], scale_log2, nl.y));
+          pf[ch * 32 + c4 * 4 + 2] = ex2(fmaf(pf[ch * 32 + c4 * 4 + 2], scale_log2, nl.z));
+          pf[ch * 32 + c4 * 4 + 3] = ex2(fmaf(pf[ch * 32 + c4 * 4 + 3], scale_log2, nl.w));
         }
         if (need_mask) {
           const uint32_t mb = static_cast<uint32_t>(colmask >> (ch * 32));
@@ -469,22 +503,23 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
       mbar_wait(dp_full, it & 1);
       tc_fence_after();
       if (it > 0) mbar_wait(ds_empty, (it - 1) & 1);   // dK / dQ MMAs of the previous tile have read sDs
+      uint32_t dpr[2][32];
+      tmem_ld32(tDP, dpr[0]);
+      tmem_ld32(tDP + 32, dpr[1]);
+      tmem_wait_ld();
 #pragma unroll
       for (int ch = 0; ch < 2; ++ch) {
-        uint32_t r[32];
-        tmem_ld32(tDP + ch * 32, r);
-        tmem_wait_ld();
         uint32_t dsp[16];
         const uint32_t kb = static_cast<uint32_t>(keepbits >> (ch * 32));
 #pragma unroll
         for (int c4 = 0; c4 < 8; ++c4) {
-          const float4 dd = *reinterpret_cast<const float4*>(d_s + ch * 32 + c4 * 4);
+          const float4 dd = lds128(d_s + (ch * 32 + c4 * 4) * 4);
           const float dsum[4] = {dd.x, dd.y, dd.z, dd.w};
           float dsv[4];
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
             const int c = c4 * 4 + e;
-            float dp = __uint_as_float(r[c]);
+            float dp = __uint_as_float(dpr[ch][c]);
             if (kDropout) dp = ((kb >> c) & 1u) ? dp * rp_dropout : 0.f;
             dsv[e] = pf[ch * 32 + c] * (dp - dsum[e]);
           }
@@ -587,7 +622,7 @@ __global__ void __launch_bounds__(256) bwd_preprocess_kernel(const fa_params p, 
 }
 
 // ------------------------------------------------------------------------------------------------
-// postprocess: dq = scale * dq_accum (tile layout [DPAD/4][128 rows][4]) -> 16 bit, caller's strides
+// postprocess: dq = scale * dq_accum (tile layout [4 row quarters][DPAD/4][32 rows][4]) -> 16 bit, caller's strides
 // ------------------------------------------------------------------------------------------------
 template <bool kBf16, int DPAD>
 __global__ void __launch_bounds__(256) bwd_postprocess_kernel(const fa_params p, const BwdWs ws) {
@@ -606,7 +641,8 @@ __global__ void __launch_bounds__(256) bwd_postprocess_kernel(const fa_params p,
     if (col >= p.d) break;
     float4 v[4];
 #pragma unroll
-    for (int gq = 0; gq < 4; ++gq) v[gq] = *reinterpret_cast<const float4*>(tile + (col / 4 + gq) * 512 + r * 4);
+    for (int gq = 0; gq < 4; ++gq)
+      v[gq] = *reinterpret_cast<const float4*>(tile + (r >> 5) * (32 * DPAD) + (col / 4 + gq) * 128 + (r & 31) * 4);
     uint4 a, b;
     a.x = pack2<kBf16>(v[0].x * sc, v[0].y * sc);
     a.y = pack2<kBf16>(v[0].z * sc, v[0].w * sc);
