@@ -44,9 +44,9 @@ struct BwdSmem {
   static constexpr int kQOff = kVOff + kTile;             // 2 stages
   static constexpr int kDoOff = kQOff + 2 * kTile;        // 1 stage
   static constexpr int kDsOff = kDoOff + kTile;           // dS^T: [128 keys x 128 queries] 16 bit
-  static constexpr int kDqOff = kDsOff + 2 * kSub;        // dQ staging: 2 x 8 KB
-  static constexpr int kDqStageBytes = 8192;
-  static constexpr int kStatOff = kDqOff + 2 * kDqStageBytes;   // 2 stages x { -lse*log2e [128], D [128] } fp32
+  static constexpr int kDqBufs = 3;                       // dQ staging: per drain warp a ring of 2 KB buffers
+  static constexpr int kDqOff = kDsOff + 2 * kSub;
+  static constexpr int kStatOff = kDqOff + 4 * kDqBufs * 2048;   // 2 stages x { -lse*log2e [128], D [128] } fp32
   static constexpr int kMaskOff = kStatOff + 2 * 1024;    // dropout keep bits: 2 x [4 key words][128 queries] u32
   static constexpr int kListOff = kMaskOff + 2 * 2048;    // blocksparse: int16 list[512], uint8 flags[512]
   static constexpr int kBarOff = kListOff + kMaxSparseTiles * 3;
@@ -67,6 +67,24 @@ struct BwdWs {
   float* dq_accum;   // (b*h, n_qtiles, 4 row quarters, DPAD/4, 32, 4) fp32
   int sq_pad, n_qtiles;
 };
+
+// Optional timeline tracing of one CTA (build with -DFA_BWD_TRACE; tools/trace_bwd.py): clock64 at pipeline events.
+#ifdef FA_BWD_TRACE
+__device__ long long g_bwd_trace[64 * 32];
+__device__ long long g_bwd_cta[8192 * 8];   // per CTA: smid, globaltimer start, clock start, after setup, compute loop end, epilogue end, globaltimer end
+#define FA_CTA_MARK(slot, val)                                                            \
+  do {                                                                                    \
+    const int cta_lin = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);   \
+    if (cta_lin < 8192) g_bwd_cta[cta_lin * 8 + (slot)] = (val);                          \
+  } while (0)
+#define FA_TRACE(slot)                                                                                   \
+  do {                                                                                                   \
+    if (trace_cta && it < 64 && (threadIdx.x & 31) == 0) g_bwd_trace[it * 32 + (slot)] = clock64();      \
+  } while (0)
+#else
+#define FA_TRACE(slot) do { } while (0)
+#define FA_CTA_MARK(slot, val) do { } while (0)
+#endif
 
 __device__ __forceinline__ float4 lds128(uint32_t addr) {
   float4 v;
@@ -91,8 +109,20 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
   const int bidb = blockIdx.z, bidh = blockIdx.y, n_blk = blockIdx.x;
   const SeqInfo seq(p.cu_seqlens_q, p.cu_seqlens_k, bidb);
   const int k0 = n_blk * kBN;
+#ifdef FA_BWD_TRACE
+  if (threadIdx.x == 0) {
+    uint32_t smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    FA_CTA_MARK(0, (long long)smid);
+    FA_CTA_MARK(1, (long long)global_timer_ns());
+    FA_CTA_MARK(2, clock64());
+  }
+#endif
   if (k0 >= seq.seqlen_k) return;   // CTA-uniform: no key rows to produce
   const uint32_t bh = bidb * p.h + bidh;
+#ifdef FA_BWD_TRACE
+  const bool trace_cta = blockIdx.x == 1 && blockIdx.y == 0 && blockIdx.z == 0;
+#endif
 
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
   uint64_t* k_full = bars + 0;
@@ -176,6 +206,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  if (threadIdx.x == 0) FA_CTA_MARK(3, clock64());
 
   uint8_t* sK = smem + L::kKOff;
   uint8_t* sV = smem + L::kVOff;
@@ -209,6 +240,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
           const int m = tile_of(it);
           const int s = it & 1;
           mbar_wait(&q_empty[s], ((it >> 1) & 1) ^ 1);
+          FA_TRACE(20);
           mbar_arrive_expect_tx(&q_full[s], L::kTile + 1024);
 #pragma unroll
           for (int c = 0; c < DPAD / 64; ++c)
@@ -217,6 +249,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
           bulk_load_1d(sStat + s * 256, ws.nl + stat_off, 512, &q_full[s]);
           bulk_load_1d(sStat + s * 256 + 128, ws.dsum + stat_off, 512, &q_full[s]);
           mbar_wait(do_empty, (it & 1) ^ 1);
+          FA_TRACE(21);
           mbar_arrive_expect_tx(do_full, L::kTile);
 #pragma unroll
           for (int c = 0; c < DPAD / 64; ++c)
@@ -225,118 +258,161 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
       }
     } else if (warp == 12) {
       // ===================================== MMA issuer ========================================
-      if (elect_one() && n_iter > 0) {
+      // All 32 lanes run the control flow (waits, loop counters, descriptor arithmetic stay warp-uniform, so the
+      // compiler keeps them on the uniform datapath); only the elected lane issues tcgen05.mma / tcgen05.commit.
+      if (n_iter > 0) {
+        const bool leader = lane == 0;
         const uint32_t idesc_st = make_idesc_f16(kBf16, 128, 128, false, false);    // S^T, dP^T
         const uint32_t idesc_kv = make_idesc_f16(kBf16, 128, DPAD, false, true);    // dV, dK (B = dO / Q, MN-major)
         const uint32_t idesc_dq = make_idesc_f16(kBf16, 128, DPAD, true, true);     // dQ (A = dS^T read MN-major)
-        const uint32_t aK = smem_u32(sK), aV = smem_u32(sV), aQ = smem_u32(sQ), aDo = smem_u32(sDo), aDs = smem_u32(sDs);
+        const uint32_t aQ = smem_u32(sQ);
         const uint32_t tS = tmem_base + kColS, tDP = tmem_base + kColDP, tDV = tmem_base + kColDV, tDK = tmem_base + kColDK;
+        // descriptor bases; a byte offset o inside a tile is added as (o >> 4) to the low word
+        const uint64_t dK_k = make_smem_desc_sw128(smem_u32(sK), 16, 1024);          // K-major view (SBO = 8 rows)
+        const uint64_t dV_k = make_smem_desc_sw128(smem_u32(sV), 16, 1024);
+        const uint64_t dQ_k = make_smem_desc_sw128(aQ, 16, 1024);
+        const uint64_t dDo_k = make_smem_desc_sw128(smem_u32(sDo), 16, 1024);
+        const uint64_t dDs_k = make_smem_desc_sw128(smem_u32(sDs), 16, 1024);
+        const uint64_t dK_mn = make_smem_desc_sw128(smem_u32(sK), L::kSub, 1024);    // MN-major view (LBO = next 64 columns)
+        const uint64_t dQ_mn = make_smem_desc_sw128(aQ, L::kSub, 1024);
+        const uint64_t dDo_mn = make_smem_desc_sw128(smem_u32(sDo), L::kSub, 1024);
+        const uint64_t dDs_mn = make_smem_desc_sw128(smem_u32(sDs), L::kSub, 1024);
+        constexpr uint32_t kQStage = L::kTile >> 4;   // descriptor units between the two Q stages
 
         // D[keys x queries] = A[keys x d] B[queries x d]^T, both K-major
-        auto issue_t = [&](uint32_t d_tmem, uint32_t a_base, uint32_t b_base) {
+        auto issue_t = [&](uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc) {
+          if (leader) {
 #pragma unroll
-          for (int kk = 0; kk < DPAD / 16; ++kk) {
-            const uint32_t off = (kk >> 2) * L::kSub + (kk & 3) * 32;
-            umma_ss(d_tmem, make_smem_desc_sw128(a_base + off, 16, 1024), make_smem_desc_sw128(b_base + off, 16, 1024),
-                    idesc_st, kk > 0 ? 1u : 0u);
+            for (int kk = 0; kk < DPAD / 16; ++kk) {
+              const uint32_t off = ((kk >> 2) * L::kSub + (kk & 3) * 32) >> 4;
+              umma_ss(d_tmem, a_desc + off, b_desc + off, idesc_st, kk > 0 ? 1u : 0u);
+            }
           }
         };
         // dV[keys x d] += P^T[keys x queries] (TMEM, 16 bit) dO[queries x d]
         auto issue_dv = [&](bool acc) {
+          if (leader) {
 #pragma unroll
-          for (int kk = 0; kk < kBM / 16; ++kk) {
-            const uint32_t a_col = (kk < 4) ? kk * 8 : 64 + (kk - 4) * 8;   // warpgroup 1's half lives at column 64
-            umma_ts(tDV, tS + a_col, make_smem_desc_sw128(aDo + kk * 2048, L::kSub, 1024), idesc_kv,
-                    (acc || kk > 0) ? 1u : 0u);
+            for (int kk = 0; kk < kBM / 16; ++kk) {
+              const uint32_t a_col = (kk < 4) ? kk * 8 : 64 + (kk - 4) * 8;   // warpgroup 1's half lives at column 64
+              umma_ts(tDV, tS + a_col, dDo_mn + (kk * 2048 >> 4), idesc_kv, (acc || kk > 0) ? 1u : 0u);
+            }
           }
         };
         // dK[keys x d] += dS^T[keys x queries] (smem, K-major) Q[queries x d] (MN-major)
-        auto issue_dk = [&](uint32_t q_base, bool acc) {
+        auto issue_dk = [&](uint32_t q_stage, bool acc) {
+          if (leader) {
 #pragma unroll
-          for (int kk = 0; kk < kBM / 16; ++kk) {
-            const uint32_t off = (kk >> 2) * L::kSub + (kk & 3) * 32;
-            umma_ss(tDK, make_smem_desc_sw128(aDs + off, 16, 1024), make_smem_desc_sw128(q_base + kk * 2048, L::kSub, 1024),
-                    idesc_kv, (acc || kk > 0) ? 1u : 0u);
+            for (int kk = 0; kk < kBM / 16; ++kk) {
+              const uint32_t off = ((kk >> 2) * L::kSub + (kk & 3) * 32) >> 4;
+              umma_ss(tDK, dDs_k + off, dQ_mn + (q_stage * kQStage + (kk * 2048 >> 4)), idesc_kv, (acc || kk > 0) ? 1u : 0u);
+            }
           }
         };
         // dQ[queries x d] = dS[queries x keys] (= dS^T tile read MN-major) K[keys x d] (MN-major)
         auto issue_dq = [&]() {
+          if (leader) {
 #pragma unroll
-          for (int kk = 0; kk < kBN / 16; ++kk) {
-            umma_ss(tDP, make_smem_desc_sw128(aDs + kk * 2048, L::kSub, 1024),
-                    make_smem_desc_sw128(aK + kk * 2048, L::kSub, 1024), idesc_dq, kk > 0 ? 1u : 0u);
+            for (int kk = 0; kk < kBN / 16; ++kk)
+              umma_ss(tDP, dDs_mn + (kk * 2048 >> 4), dK_mn + (kk * 2048 >> 4), idesc_dq, kk > 0 ? 1u : 0u);
           }
+        };
+        auto commit = [&](uint64_t* bar) {
+          if (leader) umma_commit(bar);
+        };
+        // non-blocking poll, decided by lane 0 so that the warp's control flow stays uniform
+        auto poll0 = [&](uint64_t* bar, uint32_t parity) -> bool {
+          return __shfl_sync(0xffffffffu, mbar_test_wait(bar, parity) ? 1 : 0, 0) != 0;
         };
 
         mbar_wait(k_full, 0);
         mbar_wait(&q_full[0], 0);
         tc_fence_after();
-        issue_t(tS, aK, aQ);
-        umma_commit(s_full);
+        issue_t(tS, dK_k, dQ_k);
+        commit(s_full);
         mbar_wait(v_full, 0);
         mbar_wait(do_full, 0);
         tc_fence_after();
-        issue_t(tDP, aV, aDo);
-        umma_commit(dp_full);
+        issue_t(tDP, dV_k, dDo_k);
+        commit(dp_full);
         // software pipeline: slot `it` issues  dQ(it), dK(it) | dV(it+1) | dP(it+1) | S(it+2).  dQ aliases the dP^T
         // columns, so dP(it+1) has to wait for the drain of dQ(it); dV(it+1) and dK(it) fill that gap.
         mbar_wait(p_full, 0);
         tc_fence_after();
         issue_dv(false);
-        umma_commit(do_empty);
+        commit(do_empty);
         if (n_iter > 1) {
           mbar_wait(&q_full[1], 0);
           tc_fence_after();
-          issue_t(tS, aK, aQ + L::kTile);
-          umma_commit(s_full);
+          issue_t(tS, dK_k, dQ_k + kQStage);
+          commit(s_full);
         }
         for (int it = 0; it < n_iter; ++it) {
           const int s = it & 1;
           mbar_wait(ds_full, it & 1);
+          FA_TRACE(0);
           tc_fence_after();
           issue_dq();
-          umma_commit(dq_full);
-          issue_dk(aQ + s * L::kTile, it > 0);
-          umma_commit(&q_empty[s]);
-          umma_commit(ds_empty);
+          FA_TRACE(6);
+          commit(dq_full);
+          FA_TRACE(7);
+          issue_dk(s, it > 0);
+          commit(&q_empty[s]);
+          commit(ds_empty);
+          FA_TRACE(1);
           if (it + 1 < n_iter) {
             mbar_wait(do_full, (it + 1) & 1);
-            mbar_wait(p_full, (it + 1) & 1);
-            tc_fence_after();
-            issue_dv(true);
-            mbar_wait(dq_empty, it & 1);
-            tc_fence_after();
-            issue_t(tDP, aV, aDo);
-            umma_commit(dp_full);
-            umma_commit(do_empty);
+            // dV(it+1) needs P(it+1) from the compute warps, dP(it+1) needs dQ(it) drained out of the aliased columns:
+            // issue whichever becomes ready first, then the other.
+            bool dv_done = false, dp_done = false;
+            while (!(dv_done && dp_done)) {
+              if (!dv_done && (dp_done ? (mbar_wait(p_full, (it + 1) & 1), true) : poll0(p_full, (it + 1) & 1))) {
+                FA_TRACE(2);
+                tc_fence_after();
+                issue_dv(true);
+                dv_done = true;
+              }
+              if (!dp_done && (dv_done ? (mbar_wait(dq_empty, it & 1), true) : poll0(dq_empty, it & 1))) {
+                FA_TRACE(3);
+                tc_fence_after();
+                issue_t(tDP, dV_k, dDo_k);
+                commit(dp_full);
+                dp_done = true;
+                FA_TRACE(4);
+              }
+            }
+            commit(do_empty);
             if (it + 2 < n_iter) {
               mbar_wait(&q_full[s], ((it + 2) >> 1) & 1);
               tc_fence_after();
-              issue_t(tS, aK, aQ + s * L::kTile);
-              umma_commit(s_full);
+              issue_t(tS, dK_k, dQ_k + s * kQStage);
+              commit(s_full);
+              FA_TRACE(5);
             }
           }
         }
-        umma_commit(dkv_full);
+        commit(dkv_full);
+        __syncwarp();
       }
     }
   } else if (warp >= 8) {
     // ===================================== dQ drain warps ======================================
     // Each warp drains its own 32 query rows: TMEM -> registers (up to kRing 16-column chunks in flight, so the
     // TMEM columns are handed back to the MMA warp long before the last chunk reaches global memory) -> a private
-    // 2 x 2 KB staging ring -> one 2 KB cp.reduce.async.bulk per chunk.  No CTA-wide barrier is involved.
+    // ring of 2 KB staging buffers -> one 2 KB cp.reduce.async.bulk per chunk.  No CTA-wide barrier is involved.
     setmaxnreg_dec<kDrainRegs>();
     const int wq = warp & 3;
     const uint32_t tDQ = tmem_base + (static_cast<uint32_t>(wq * 32) << 16) + kColDP;
-    uint8_t* stage_gen = sDq + wq * 4096;
+    uint8_t* stage_gen = sDq + wq * (L::kDqBufs * 2048);
     const uint32_t stage = smem_u32(stage_gen);
     constexpr int kChunks = DPAD / 16;
     constexpr int kRing = kChunks < 4 ? kChunks : 4;
-    bool primed = false;
+    uint32_t n_issued = 0;
     for (int it = 0; it < n_iter; ++it) {
       const int m = tile_of(it);
       float* gdst = ws.dq_accum + ((int64_t)bh * ws.n_qtiles + m) * (kBM * DPAD) + wq * (32 * DPAD);
       mbar_wait(dq_full, it & 1);
+      if (wq == 0) FA_TRACE(16);
       tc_fence_after();
       uint32_t v[kRing][16];
 #pragma unroll
@@ -348,12 +424,14 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
       }
 #pragma unroll
       for (int k = 0; k < kChunks; ++k) {
-        const uint32_t buf = k & 1;
-        if (primed || k >= 2) {
-          if (lane == 0) bulk_wait_group_read<1>();   // the bulk op that last read this buffer is done with it
+        const uint32_t buf = n_issued % L::kDqBufs;
+        if (n_issued >= L::kDqBufs) {
+          if (lane == 0) bulk_wait_group_read<L::kDqBufs - 1>();   // the bulk op that last read this buffer is done with it
           __syncwarp();
         }
+        ++n_issued;
         const uint32_t dst = stage + buf * 2048 + lane * 16;
+#ifndef FA_BWD_EXP_NO_DRAIN
 #pragma unroll
         for (int g = 0; g < 4; ++g)
           st_shared_v4(dst + g * 512, v[k % kRing][4 * g], v[k % kRing][4 * g + 1], v[k % kRing][4 * g + 2], v[k % kRing][4 * g + 3]);
@@ -363,16 +441,21 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
           bulk_reduce_add_f32(gdst + k * 512, stage_gen + buf * 2048, 2048);
           bulk_commit_group();
         }
+#else
+        if (v[k % kRing][0] == 0x7fc12345u) st_shared_v4(dst, 0, 0, 0, 0);   // timing experiment: no staging, no reduction
+        if (lane == 0) bulk_commit_group();
+#endif
         if (k + kRing < kChunks) {
           tmem_ld16(tDQ + (k + kRing) * 16, v[k % kRing]);
           tmem_wait_ld();
           if (k + kRing == kChunks - 1) {
             tc_fence_before();
             mbar_arrive(dq_empty);
+            if (wq == 0) FA_TRACE(17);
           }
         }
       }
-      primed = true;
+      if (wq == 0) FA_TRACE(18);
     }
     if (lane == 0) bulk_wait_group<0>();
   } else {
@@ -452,8 +535,10 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
         colmask &= e;
       }
 
-      mbar_wait(&q_full[s], (it >> 1) & 1);   // -lse*log2e and D of this tile are in shared memory
+      // s_full also covers the tile's -lse*log2e / D vectors: they complete on the same mbarrier as Q, which the MMA
+      // warp observed before issuing S^T (TMA -> q_full -> MMA issue -> commit -> s_full is a release/acquire chain)
       mbar_wait(s_full, it & 1);
+      if (wq == 0) FA_TRACE(8 + 4 * g);
       tc_fence_after();
 
       // ---- P^T = exp2(S^T * scale*log2e - lse*log2e); keep fp32 P for dS, write (P o Z) as 16 bit for dV ----
@@ -498,9 +583,11 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
       tmem_wait_st();
       tc_fence_before();
       mbar_arrive(p_full);
+      if (wq == 0) FA_TRACE(9 + 4 * g);
 
       // ---- dS^T = P^T o (dP^T o Z / keep - D), 16 bit, into swizzled shared memory ----
       mbar_wait(dp_full, it & 1);
+      if (wq == 0) FA_TRACE(10 + 4 * g);
       tc_fence_after();
       if (it > 0) mbar_wait(ds_empty, (it - 1) & 1);   // dK / dQ MMAs of the previous tile have read sDs
       uint32_t dpr[2][32];
@@ -535,9 +622,11 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
       tc_fence_before();
       fence_proxy_async();
       mbar_arrive(ds_full);
+      if (wq == 0) FA_TRACE(11 + 4 * g);
     }
 
     // ---- epilogue: warpgroup 0 stores dV (x 1/keep), warpgroup 1 stores dK (x scale) ----
+    if (threadIdx.x == 0) FA_CTA_MARK(4, clock64());
     {
       using T = typename Elem<kBf16>::T;
       if (n_iter > 0) {
@@ -582,6 +671,12 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
   }
+#ifdef FA_BWD_TRACE
+  if (threadIdx.x == 0) {
+    FA_CTA_MARK(5, clock64());
+    FA_CTA_MARK(6, (long long)global_timer_ns());
+  }
+#endif
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -714,6 +809,15 @@ cudaError_t dispatch_bwd_flags(const BwdTensorMaps& maps, const fa_params& p, co
 }  // namespace
 
 uint64_t bwd_sm100_workspace_bytes(const fa_params& p) { return bwd_ws_layout(p).total; }
+
+#ifdef FA_BWD_TRACE
+extern "C" __attribute__((visibility("default"))) int fa_debug_read_bwd_trace(long long* host, int n) {
+  return (int)cudaMemcpyFromSymbol(host, g_bwd_trace, sizeof(long long) * n);
+}
+extern "C" __attribute__((visibility("default"))) int fa_debug_read_bwd_cta(long long* host, int n) {
+  return (int)cudaMemcpyFromSymbol(host, g_bwd_cta, sizeof(long long) * n);
+}
+#endif
 
 cudaError_t launch_bwd_sm100(const fa_params& p, const BlockMaskView& bm, void* workspace, cudaStream_t stream,
                              const char** err_msg) {

@@ -51,6 +51,18 @@ FA_DEVICE bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// non-blocking probe (try_wait may suspend the thread for a hardware-defined time; test_wait never does)
+FA_DEVICE bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred P;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
+      "selp.b32 %0, 1, 0, P;\n\t}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
 // A wait that has not completed after FA_WAIT_TIMEOUT_NS traps instead of hanging the GPU: a protocol bug then
 // surfaces as a launch failure the host can report.  The timer is only read after a failed poll.
 #ifndef FA_WAIT_TIMEOUT_NS
@@ -63,9 +75,16 @@ FA_DEVICE uint64_t global_timer_ns() {
 }
 FA_DEVICE void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
-  const uint64_t t0 = global_timer_ns();
+  // try_wait suspends the thread in hardware for a bounded time; the (slow) global timer is only consulted every
+  // 256 failed polls so that it never sits between an arrival and the wake-up.
+  uint64_t t0 = 0;
+  uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (global_timer_ns() - t0 > FA_WAIT_TIMEOUT_NS) { asm volatile("trap;\n"); }
+    if ((++spins & 255u) == 0) {
+      const uint64_t now = global_timer_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > FA_WAIT_TIMEOUT_NS) { asm volatile("trap;\n"); }
+    }
   }
 }
 

@@ -14,7 +14,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB_PATH = os.path.join(_HERE, "csrc", "libfa_b200.so")
+_LIB_PATH = os.environ.get("FA_B200_LIB") or os.path.join(_HERE, "csrc", "libfa_b200.so")   # override: debug builds only
 
 FA_IMPL_AUTO, FA_IMPL_TCGEN05, FA_IMPL_SIMT = 0, 1, 2
 FA_OP_FWD, FA_OP_BWD, FA_OP_FWD_BLOCK, FA_OP_BWD_BLOCK = 0, 1, 2, 3

@@ -10,7 +10,7 @@ using namespace fa;
 constexpr int kSub = 16384;
 
 // variant: 0 SS K/K   1 SS K/MN   2 SS MN/MN   3 TS ./MN   4 TS ./K   5 SS K/K N=256   6 bwd mix (S,dP,dV,dK,dQ)  7 SS K/K N=64
-__global__ void __launch_bounds__(256, 1) mma_bench_kernel(int variant, int reps, int traffic_warps, long long* out) {
+__global__ void __launch_bounds__(256, 1) mma_bench_kernel(int variant, int reps, int traffic_warps, int random_data, long long* out) {   // random_data: bit0 random operands, bit1 TMEM-load traffic, bit2 + TMEM stores
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   __shared__ uint64_t bar;
@@ -18,7 +18,13 @@ __global__ void __launch_bounds__(256, 1) mma_bench_kernel(int variant, int reps
   __shared__ int stop_flag;
   const int warp = threadIdx.x >> 5;
   // zero operands (4 tiles of 32 KB)
-  for (int i = threadIdx.x; i < 4 * 32768 / 16; i += blockDim.x) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = threadIdx.x; i < 4 * 32768 / 4; i += blockDim.x) {
+    // random bf16 pairs in (-2, 2): sign + exponent 0x3f.. + random mantissa
+    uint32_t h = (i * 2654435761u) ^ (blockIdx.x * 40503u);
+    h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
+    const uint32_t lo = 0x3f00u | (h & 0x80ffu), hi = 0x3f00u | ((h >> 16) & 0x80ffu);
+    reinterpret_cast<uint32_t*>(smem)[i] = (random_data & 1) ? (lo | (hi << 16)) : 0u;
+  }
   if (threadIdx.x == 0) {
     mbar_init(&bar, 1);
     fence_mbar_init();
@@ -96,6 +102,16 @@ __global__ void __launch_bounds__(256, 1) mma_bench_kernel(int variant, int reps
     // concurrent shared-memory store traffic (16 B per lane per store, conflict free) in a scratch region after the operands
     const uint32_t dst = a0 + 131072 + (threadIdx.x & 1023) * 16;
     volatile int* sf = &stop_flag;
+    if (random_data & 2) {
+      // TMEM traffic instead: every warp reads (bit 2: also writes back) 32 columns of its lane quarter in a loop
+      const uint32_t t = tm + (static_cast<uint32_t>((warp & 3) * 32) << 16) + 448;
+      uint32_t r[32];
+      while (*sf == 0) {
+        tmem_ld32(t, r);
+        tmem_wait_ld();
+        if (random_data & 4) { tmem_st32(t + 32, r); tmem_wait_st(); }
+      }
+    } else
     while (*sf == 0) {
 #pragma unroll
       for (int i = 0; i < 8; ++i)
@@ -117,15 +133,15 @@ int main() {
   cudaFuncSetAttribute(mma_bench_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   const char* names[] = {"SS K/K N128", "SS K/MN N128", "SS MN/MN N128", "TS ./MN N128", "TS ./K N128", "SS K/K N256", "bwd mix (5 tiles)", "SS K/K N64"};
   const int reps = 200;
-  for (int traffic = 0; traffic <= 4; traffic += 2) {
+  for (int traffic : {8, 12, 8 + 16 + 4, 8 + 16 + 7, 8 + 16 + 32 + 4, 8 + 16 + 32 + 7}) {   // bit 3: random operand data; low bits: store-traffic warps
     for (int v = 0; v < 8; ++v) {
-      mma_bench_kernel<<<148, 256, smem>>>(v, reps, traffic, out);
+      mma_bench_kernel<<<148, 256, smem>>>(v, reps, traffic & 7, traffic >> 3, out);
       cudaError_t e = cudaDeviceSynchronize();
       if (e != cudaSuccess) { printf("variant %d failed: %s\n", v, cudaGetErrorString(e)); return 1; }
       long long cyc;
       cudaMemcpy(&cyc, out, 8, cudaMemcpyDeviceToHost);
       const int n_instr = reps * 8 * (v == 6 ? 5 : 1);
-      printf("traffic_warps=%d  %-18s  %8.1f clk / MMA instr  (%.0f clk per 128x128x128 tile)\n", traffic, names[v],
+      printf("cfg=%2d (random=%d, traffic warps=%d)  %-18s  %8.1f clk / MMA instr  (%.0f clk per 128x128x128 tile)\n", traffic, traffic >> 3, traffic & 7, names[v],
              (double)cyc / n_instr, (double)cyc / n_instr * 8);
     }
   }
