@@ -138,6 +138,58 @@ __global__ void scatter_rows_kernel(V* __restrict__ dst, const V* __restrict__ s
   }
 }
 
+// Ring / split-KV merge of two partial attention results over the same queries (the reference's inter-K-block rule,
+// src/fmha_fprop_kernel_1xN.h:606-650, lifted to whole blocks):
+//     lse' = log(exp(lse) + exp(lse_blk));   o' = o * exp(lse - lse') + o_blk * exp(lse_blk - lse')
+// o_acc fp32 (rows, h, d) contiguous, o_blk 16 bit (rows, h, d) contiguous; lse (b, h, stride) with rows = b * seqlen.
+// One thread per 8 head-dim elements; `first` = initialise the accumulator from the block.  The merged lse goes to a
+// second buffer (same shape as lse_acc; must not alias it) so that no thread can observe a half-updated row.
+template <bool kBf16>
+__global__ void __launch_bounds__(256) merge_partials_kernel(float* __restrict__ o_acc, const float* __restrict__ lse_acc, float* __restrict__ lse_out,
+                                                             const void* __restrict__ o_blk_, const float* __restrict__ lse_blk,
+                                                             int b, int h, int d, int seqlen, int acc_stride, int blk_stride,
+                                                             int first) {
+  using T = typename Elem<kBf16>::T;
+  const int d8 = d >> 3;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t total = (int64_t)b * seqlen * h * d8;
+  if (idx >= total) return;
+  const int c8 = static_cast<int>(idx % d8);
+  const int hh = static_cast<int>((idx / d8) % h);
+  const int64_t row = idx / ((int64_t)d8 * h);
+  const int bi = static_cast<int>(row / seqlen), t = static_cast<int>(row % seqlen);
+  const int64_t ia = ((int64_t)bi * h + hh) * acc_stride + t, ib = ((int64_t)bi * h + hh) * blk_stride + t;
+  const float lb = lse_blk[ib];
+  const float la = first ? -INFINITY : lse_acc[ia];
+  const float mx = fmaxf(la, lb);
+  float wa = 0.f, wb = 0.f, ln = -INFINITY;
+  if (mx != -INFINITY) {
+    const float ea = __expf(la - mx), eb = __expf(lb - mx);
+    ln = mx + __logf(ea + eb);
+    wa = ea / (ea + eb);
+    wb = eb / (ea + eb);
+  }
+  const int64_t off = (row * h + hh) * d + c8 * 8;
+  const uint4 raw = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(o_blk_) + off));
+  const T* e = reinterpret_cast<const T*>(&raw);
+  float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+  if (!first) {
+    a0 = *reinterpret_cast<const float4*>(o_acc + off);
+    a1 = *reinterpret_cast<const float4*>(o_acc + off + 4);
+  }
+  a0.x = a0.x * wa + Elem<kBf16>::to_float(e[0]) * wb;
+  a0.y = a0.y * wa + Elem<kBf16>::to_float(e[1]) * wb;
+  a0.z = a0.z * wa + Elem<kBf16>::to_float(e[2]) * wb;
+  a0.w = a0.w * wa + Elem<kBf16>::to_float(e[3]) * wb;
+  a1.x = a1.x * wa + Elem<kBf16>::to_float(e[4]) * wb;
+  a1.y = a1.y * wa + Elem<kBf16>::to_float(e[5]) * wb;
+  a1.z = a1.z * wa + Elem<kBf16>::to_float(e[6]) * wb;
+  a1.w = a1.w * wa + Elem<kBf16>::to_float(e[7]) * wb;
+  *reinterpret_cast<float4*>(o_acc + off) = a0;
+  *reinterpret_cast<float4*>(o_acc + off + 4) = a1;
+  if (c8 == 0) lse_out[ia] = ln;   // separate buffer: the other threads of this (row, head) still read lse_acc
+}
+
 template <bool kGather>
 int move_rows(void* dst, const void* src, const int64_t* indices, int64_t n, int64_t row_bytes, void* stream) {
   if (n < 0 || row_bytes < 0) return fail(FA_ERR_INVALID_ARGUMENT, "negative size");
@@ -332,6 +384,28 @@ int fa_fwd(const fa_params* p, void* stream) { return fa::run_fwd(p, stream, fal
 int fa_bwd(const fa_params* p, void* stream) { return fa::run_bwd(p, stream, false); }
 int fa_fwd_block(const fa_params* p, void* stream) { return fa::run_fwd(p, stream, true); }
 int fa_bwd_block(const fa_params* p, void* stream) { return fa::run_bwd(p, stream, true); }
+
+int fa_merge_partials(float* o_acc, const float* lse_acc, float* lse_out, const void* o_blk, const float* lse_blk, int32_t b, int32_t h, int32_t d,
+                      int32_t seqlen, int32_t lse_acc_stride, int32_t lse_blk_stride, int32_t is_bf16, int32_t first,
+                      void* stream) {
+  fa::g_last_error[0] = 0;
+  if (b <= 0 || h <= 0 || seqlen < 0 || d <= 0 || d % 8 != 0)
+    return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_merge_partials: bad sizes (b %d, h %d, d %d, seqlen %d)", b, h, d, seqlen);
+  if (seqlen == 0) return FA_OK;
+  if (!o_acc || !lse_acc || !lse_out || lse_out == lse_acc || !o_blk || !lse_blk) return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_merge_partials: NULL or aliased pointer");
+  if (lse_acc_stride < seqlen || lse_blk_stride < seqlen) return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_merge_partials: lse stride < seqlen");
+  int rc = fa::check_device();
+  if (rc != FA_OK) return rc;
+  const int64_t total = (int64_t)b * seqlen * h * (d / 8);
+  const unsigned grid = static_cast<unsigned>((total + 255) / 256);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (is_bf16) fa::merge_partials_kernel<true><<<grid, 256, 0, st>>>(o_acc, lse_acc, lse_out, o_blk, lse_blk, b, h, d, seqlen, lse_acc_stride, lse_blk_stride, first);
+  else fa::merge_partials_kernel<false><<<grid, 256, 0, st>>>(o_acc, lse_acc, lse_out, o_blk, lse_blk, b, h, d, seqlen, lse_acc_stride, lse_blk_stride, first);
+  fa::count_launch();
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fa::cuda_fail(e, "merge_partials launch");
+  return FA_OK;
+}
 
 int fa_gather_rows(void* dst, const void* src, const int64_t* indices, int64_t n_indices, int64_t row_bytes, void* stream) {
   fa::g_last_error[0] = 0;

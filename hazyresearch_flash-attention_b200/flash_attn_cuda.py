@@ -70,6 +70,8 @@ def _load_library():
         fn.restype = ctypes.c_int
         fn.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64,
                        ctypes.c_void_p]
+    lib.fa_merge_partials.restype = ctypes.c_int
+    lib.fa_merge_partials.argtypes = [ctypes.c_void_p] * 5 + [ctypes.c_int32] * 8 + [ctypes.c_void_p]
     lib.fa_dropout_keep8_host.restype = None
     lib.fa_dropout_keep8_host.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint32,
                                           ctypes.c_uint32, ctypes.c_float, ctypes.c_void_p]
@@ -335,6 +337,24 @@ def scatter_rows(src2d, indices, first_axis_dim):
                                   torch.cuda.current_stream().cuda_stream)
     _raise_if_failed(rc, "fa_scatter_rows")
     return out
+
+
+def merge_partials(o_acc, lse_acc, lse_out, o_blk, lse_blk, batch, seqlen, first):
+    """Ring / split-KV merge (fa_merge_partials): o_acc fp32 (batch*seqlen, h, d) updated in place, lse_out written.
+    lse tensors are (batch, h, stride) fp32; o_blk is the 16-bit block output."""
+    _check(o_acc.is_cuda and o_acc.dtype == torch.float32 and o_acc.is_contiguous(), "o_acc must be contiguous fp32 CUDA")
+    _check(o_blk.dtype in (torch.float16, torch.bfloat16) and o_blk.is_contiguous() and o_blk.shape == o_acc.shape,
+           "o_blk must be contiguous fp16/bf16 with the shape of o_acc")
+    for t in (lse_acc, lse_out, lse_blk):
+        _check(t.dtype == torch.float32 and t.is_contiguous() and t.dim() == 3, "lse tensors must be contiguous (b, h, s) fp32")
+    _check(lse_acc.shape == lse_out.shape and lse_acc.data_ptr() != lse_out.data_ptr(), "lse_out must be a distinct buffer")
+    rows, h, d = o_acc.shape
+    _check(rows == batch * seqlen, "o_acc rows != batch * seqlen")
+    with torch.cuda.device(o_acc.device):
+        rc = _lib.fa_merge_partials(_ptr(o_acc), _ptr(lse_acc), _ptr(lse_out), _ptr(o_blk), _ptr(lse_blk), batch, h, d, seqlen,
+                                    lse_acc.shape[2], lse_blk.shape[2], 1 if o_blk.dtype == torch.bfloat16 else 0,
+                                    1 if first else 0, torch.cuda.current_stream().cuda_stream)
+    _raise_if_failed(rc, "fa_merge_partials")
 
 
 def kernel_timing(enable):

@@ -129,6 +129,16 @@ int fa_gather_rows(void* dst, const void* src, const int64_t* indices, int64_t n
 int fa_scatter_rows(void* dst, const void* src, const int64_t* indices, int64_t n_indices, int64_t row_bytes,
                     void* stream);
 
+/* Merge of two partial attention results over the same queries (K/V split across ring steps / GPUs): the reference's
+ * inter-K-block rule (csrc/flash_attn/src/fmha_fprop_kernel_1xN.h:606-650) applied to whole blocks.
+ *   lse_out = log(exp(lse_acc) + exp(lse_blk));  o_acc = o_acc * exp(lse_acc - lse_out) + o_blk * exp(lse_blk - lse_out)
+ * o_acc: fp32 (b * seqlen, h, d) contiguous, updated in place; o_blk: 16-bit (b * seqlen, h, d) contiguous;
+ * lse_acc / lse_out: (b, h, lse_acc_stride) fp32, distinct buffers; lse_blk: (b, h, lse_blk_stride) fp32.
+ * first != 0: initialise (o_acc = o_blk, lse_out = lse_blk; lse_acc is not read). */
+int fa_merge_partials(float* o_acc, const float* lse_acc, float* lse_out, const void* o_blk, const float* lse_blk, int32_t b,
+                      int32_t h, int32_t d, int32_t seqlen, int32_t lse_acc_stride, int32_t lse_blk_stride, int32_t is_bf16,
+                      int32_t first, void* stream);
+
 /* Host-only helper exposing the dropout RNG for tests: fills keep[8] (0/1) for the 8 key positions
  * 8*kgroup .. 8*kgroup+7 of query row `qrow` in (batch*h + head) = bh.  Pure CPU code. */
 void fa_dropout_keep8_host(uint64_t seed, uint64_t offset, uint32_t bh, uint32_t qrow, uint32_t kgroup,
