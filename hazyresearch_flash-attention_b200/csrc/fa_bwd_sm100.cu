@@ -71,11 +71,11 @@ struct BwdWs {
 // Optional timeline tracing of one CTA (build with -DFA_BWD_TRACE; tools/trace_bwd.py): clock64 at pipeline events.
 #ifdef FA_BWD_TRACE
 __device__ long long g_bwd_trace[64 * 32];
-__device__ long long g_bwd_cta[8192 * 8];   // per CTA: smid, globaltimer start, clock start, after setup, compute loop end, epilogue end, globaltimer end
+__device__ long long g_bwd_cta[8192 * 12];   // per CTA: smid, globaltimer start, clock start, after setup, compute loop end, epilogue end, globaltimer end
 #define FA_CTA_MARK(slot, val)                                                            \
   do {                                                                                    \
     const int cta_lin = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);   \
-    if (cta_lin < 8192) g_bwd_cta[cta_lin * 8 + (slot)] = (val);                          \
+    if (cta_lin < 8192) g_bwd_cta[cta_lin * 12 + (slot)] = (val);                          \
   } while (0)
 #define FA_TRACE(slot)                                                                                   \
   do {                                                                                                   \
@@ -457,7 +457,9 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
       }
       if (wq == 0) FA_TRACE(18);
     }
-    if (lane == 0) bulk_wait_group<0>();
+    if (warp == 8 && lane == 0) FA_CTA_MARK(9, clock64());    // last chunk issued
+    if (lane == 0) bulk_wait_group_read<0>();   // the staging buffers may go away; the reductions complete on their own
+    if (warp == 8 && lane == 0) FA_CTA_MARK(10, clock64());
   } else {
     // ===================================== compute warps =======================================
     setmaxnreg_inc<kComputeRegs>();
@@ -628,41 +630,22 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     // ---- epilogue: warpgroup 0 stores dV (x 1/keep), warpgroup 1 stores dK (x scale) ----
     if (threadIdx.x == 0) FA_CTA_MARK(4, clock64());
     {
-      using T = typename Elem<kBf16>::T;
       if (n_iter > 0) {
         mbar_wait(dkv_full, 0);
+        if (threadIdx.x == 0) FA_CTA_MARK(7, clock64());
         tc_fence_after();
       }
       const uint32_t tAcc = tmem_base + lane_base + (g == 0 ? kColDV : kColDK);
       const float out_scale = g == 0 ? (kDropout ? rp_dropout : 1.f) : p.softmax_scale;
-      T* orow = g == 0 ? reinterpret_cast<T*>(p.dv) + (int64_t)(seq.k_begin + key) * p.dv_row_stride + (int64_t)bidh * p.dv_head_stride
-                       : reinterpret_cast<T*>(p.dk) + (int64_t)(seq.k_begin + key) * p.dk_row_stride + (int64_t)bidh * p.dk_head_stride;
-#pragma unroll
-      for (int c4 = 0; c4 < DPAD / 32; ++c4) {
-        uint32_t o[32];
-        if (n_iter > 0) {
-          tmem_ld32(tAcc + c4 * 32, o);
-          tmem_wait_ld();
-        } else {
-#pragma unroll
-          for (int c = 0; c < 32; ++c) o[c] = 0u;
-        }
-        if (key_valid) {
-#pragma unroll
-          for (int v8 = 0; v8 < 4; ++v8) {
-            const int col = c4 * 32 + v8 * 8;
-            if (col < p.d) {
-              uint4 pk4;
-              pk4.x = pack2<kBf16>(__uint_as_float(o[v8 * 8 + 0]) * out_scale, __uint_as_float(o[v8 * 8 + 1]) * out_scale);
-              pk4.y = pack2<kBf16>(__uint_as_float(o[v8 * 8 + 2]) * out_scale, __uint_as_float(o[v8 * 8 + 3]) * out_scale);
-              pk4.z = pack2<kBf16>(__uint_as_float(o[v8 * 8 + 4]) * out_scale, __uint_as_float(o[v8 * 8 + 5]) * out_scale);
-              pk4.w = pack2<kBf16>(__uint_as_float(o[v8 * 8 + 6]) * out_scale, __uint_as_float(o[v8 * 8 + 7]) * out_scale);
-              *reinterpret_cast<uint4*>(orow + col) = pk4;
-            }
-          }
-        }
-      }
+      // K and V tiles are dead once dkv_full has completed: each warp stages its 32 rows in its slice of them
+      const uint32_t stage = smem_u32(g == 0 ? sV : sK) + wq * (32 * DPAD * 2);
+      const int row0 = k0 + wq * 32;
+      uint16_t* grow0 = g == 0 ? reinterpret_cast<uint16_t*>(p.dv) + (int64_t)(seq.k_begin + row0) * p.dv_row_stride + (int64_t)bidh * p.dv_head_stride
+                               : reinterpret_cast<uint16_t*>(p.dk) + (int64_t)(seq.k_begin + row0) * p.dk_row_stride + (int64_t)bidh * p.dk_head_stride;
+      store_acc_rows_coalesced<DPAD, kBf16>(tAcc, n_iter > 0, out_scale, stage, grow0, g == 0 ? p.dv_row_stride : p.dk_row_stride,
+                                            min(max(seq.seqlen_k - row0, 0), 32), p.d, lane);
     }
+    if (threadIdx.x == 0) FA_CTA_MARK(8, clock64());   // dK / dV stored
   }
 
   tc_fence_before();

@@ -370,41 +370,21 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
 
     // ---- epilogue: O = acc / l (x 1/keep), lse = m*scale + ln(l) ----
     if (my_cnt > 0 || (q0 + t * kBlockM) < seq.seqlen_q) {
-      using T = typename Elem<kBf16>::T;
       const bool dead = (l == 0.f) || (l != l);
       const float inv_l = dead ? 1.f : 1.f / l;
       const float out_scale = inv_l * (kDropout ? 1.f / (1.f - p.p_dropout) : 1.f);
       const float lse = dead ? -INFINITY : (m * scale_log2 + log2f(l)) * kLn2;
-      T* orow = reinterpret_cast<T*>(p.o) + (int64_t)(seq.q_begin + qi) * p.o_row_stride + (int64_t)bidh * p.o_head_stride;
       if (my_cnt > 0) {
         mbar_wait(&o_full[t], 0);
         tc_fence_after();
       }
-#pragma unroll
-      for (int c4 = 0; c4 < DPAD / 32; ++c4) {
-        uint32_t o[32];
-        if (my_cnt > 0) {
-          tmem_ld32(tO + c4 * 32, o);
-          tmem_wait_ld();
-        } else {
-#pragma unroll
-          for (int c = 0; c < 32; ++c) o[c] = 0u;
-        }
-        if (row_valid) {
-#pragma unroll
-          for (int v8 = 0; v8 < 4; ++v8) {
-            const int col = c4 * 32 + v8 * 8;
-            if (col < p.d) {
-              uint4 pk4;
-              pk4.x = pack2<kBf16>(__uint_as_float(o[v8 * 8 + 0]) * out_scale, __uint_as_float(o[v8 * 8 + 1]) * out_scale);
-              pk4.y = pack2<kBf16>(__uint_as_float(o[v8 * 8 + 2]) * out_scale, __uint_as_float(o[v8 * 8 + 3]) * out_scale);
-              pk4.z = pack2<kBf16>(__uint_as_float(o[v8 * 8 + 4]) * out_scale, __uint_as_float(o[v8 * 8 + 5]) * out_scale);
-              pk4.w = pack2<kBf16>(__uint_as_float(o[v8 * 8 + 6]) * out_scale, __uint_as_float(o[v8 * 8 + 7]) * out_scale);
-              *reinterpret_cast<uint4*>(orow + col) = pk4;
-            }
-          }
-        }
-      }
+      // o_full also means every S = QK^T of this tile has completed, so the tile's Q buffer is free: each warp stages
+      // its 32 output rows there and writes them back as whole rows (see store_acc_rows_coalesced)
+      const int row0 = q0 + t * kBlockM + (warp & 3) * 32;
+      const uint32_t stage = smem_u32(sQ) + t * L::kTileBytes + (warp & 3) * (32 * DPAD * 2);
+      uint16_t* grow0 = reinterpret_cast<uint16_t*>(p.o) + (int64_t)(seq.q_begin + row0) * p.o_row_stride + (int64_t)bidh * p.o_head_stride;
+      store_acc_rows_coalesced<DPAD, kBf16>(tO, my_cnt > 0, out_scale, stage, grow0, p.o_row_stride,
+                                            min(max(seq.seqlen_q - row0, 0), 32), p.d, lane);
       if (row_valid) p.softmax_lse[(int64_t)bh * p.seqlen_q_rounded + qi] = lse;
     }
   }

@@ -258,6 +258,55 @@ FA_DEVICE uint32_t pack2(float lo, float hi) {   // round-to-nearest-even pack o
   }
   return r;
 }
+// ------------------------------------------------------------------------------------------------
+// Epilogue helper: one warp moves its 32 accumulator rows (TMEM lanes, DPAD fp32 columns) to global memory as 16-bit
+// rows of `d` elements.  Each lane owns one row in TMEM, which would make every global store touch 32 different
+// lines; the rows are therefore staged through 32 * DPAD * 2 bytes of shared memory (XOR-swizzled 16-byte chunks) and
+// written back with 16 / 8 lanes per row, i.e. whole 256 / 128-byte rows per store instruction.
+// `taddr`: TMEM address of this warp's lane quarter, column 0 of the accumulator.  `have_acc` = false stores zeros.
+// ------------------------------------------------------------------------------------------------
+template <int DPAD, bool kBf16>
+FA_DEVICE void store_acc_rows_coalesced(uint32_t taddr, bool have_acc, float scale, uint32_t stage, uint16_t* grow0,
+                                        int64_t row_stride, int valid_rows, int d, int lane) {
+  constexpr int kRowBytes = DPAD * 2;
+  constexpr int kChunksPerRow = DPAD / 8;             // 16-byte chunks
+  constexpr int kRowsPerInstr = 32 / kChunksPerRow;   // 2 (DPAD 128) or 4 (DPAD 64)
+#pragma unroll
+  for (int c4 = 0; c4 < DPAD / 32; ++c4) {
+    uint32_t o[32];
+    if (have_acc) {
+      tmem_ld32(taddr + c4 * 32, o);
+      tmem_wait_ld();
+    } else {
+#pragma unroll
+      for (int c = 0; c < 32; ++c) o[c] = 0u;
+    }
+#pragma unroll
+    for (int v8 = 0; v8 < 4; ++v8) {
+      const uint32_t chunk = static_cast<uint32_t>((c4 * 4 + v8) ^ (lane & 7));
+      const uint32_t a = pack2<kBf16>(__uint_as_float(o[v8 * 8 + 0]) * scale, __uint_as_float(o[v8 * 8 + 1]) * scale);
+      const uint32_t b = pack2<kBf16>(__uint_as_float(o[v8 * 8 + 2]) * scale, __uint_as_float(o[v8 * 8 + 3]) * scale);
+      const uint32_t c = pack2<kBf16>(__uint_as_float(o[v8 * 8 + 4]) * scale, __uint_as_float(o[v8 * 8 + 5]) * scale);
+      const uint32_t e = pack2<kBf16>(__uint_as_float(o[v8 * 8 + 6]) * scale, __uint_as_float(o[v8 * 8 + 7]) * scale);
+      asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(stage + lane * kRowBytes + chunk * 16), "r"(a), "r"(b),
+                   "r"(c), "r"(e)
+                   : "memory");
+    }
+  }
+  __syncwarp();
+  const int j = lane % kChunksPerRow;
+#pragma unroll
+  for (int i = 0; i < 32 / kRowsPerInstr; ++i) {
+    const int row = i * kRowsPerInstr + lane / kChunksPerRow;
+    uint4 v;
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];\n"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "r"(stage + row * kRowBytes + ((j ^ (row & 7)) * 16))
+                 : "memory");
+    if (row < valid_rows && j * 8 < d) *reinterpret_cast<uint4*>(grow0 + row * row_stride + j * 8) = v;
+  }
+}
+
 FA_DEVICE void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;\n" ::"r"(id), "r"(nthreads) : "memory");
 }

@@ -36,15 +36,17 @@ per = [T[i + 1][0] - T[i][0] for i in range(4, 24) if T[i + 1][0] > 0 and T[i][0
 print("period (M:ds_full to next):", per)
 # ---- per-CTA lifetimes ----
 ncta = min(8192, (s // 128) * h * b)
-cb = (ctypes.c_longlong * (ncta * 8))()
+cb = (ctypes.c_longlong * (ncta * 12))()
 flash_attn_cuda._lib.fa_debug_read_bwd_cta.argtypes = [ctypes.c_void_p, ctypes.c_int]
-assert flash_attn_cuda._lib.fa_debug_read_bwd_cta(cb, ncta * 8) == 0
+assert flash_attn_cuda._lib.fa_debug_read_bwd_cta(cb, ncta * 12) == 0
 import statistics
-C = [[cb[i * 8 + j] for j in range(8)] for i in range(ncta)]
+C = [[cb[i * 12 + j] for j in range(12)] for i in range(ncta)]
 C = [c for c in C if c[5] > 0]
 print("CTAs", len(C))
 print("median clk: setup %d  loop %d  epilogue %d  total %d" % (statistics.median(c[3] - c[2] for c in C), statistics.median(c[4] - c[3] for c in C),
       statistics.median(c[5] - c[4] for c in C), statistics.median(c[5] - c[2] for c in C)))
+print("epilogue median clk after loop end: dkv_full +%d  dK/dV stored +%d  drain last issue +%d  drain reads done +%d  CTA end +%d" % tuple(
+    statistics.median(c[j] - c[4] for c in C) for j in (7, 8, 9, 10, 5)))
 by_sm = {}
 for c in C:
     by_sm.setdefault(c[0], []).append(c)
