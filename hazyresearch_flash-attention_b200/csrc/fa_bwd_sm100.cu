@@ -100,13 +100,23 @@ __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t
 // ------------------------------------------------------------------------------------------------
 template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse>
 __global__ void __launch_bounds__(kBwdThreads, 1)
-bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, const BlockMaskView bm, const BwdWs ws) {
+bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, const BlockMaskView bm, const BwdWs ws,
+                 const int n_kblocks) {
   using L = BwdSmem<DPAD>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int bidb = blockIdx.z, bidh = blockIdx.y, n_blk = blockIdx.x;
+  // causal: 1-D launch, longest (lowest key block) first within groups of (batch, head) pairs; else grid (block, h, b)
+  int bidb, bidh, n_blk;
+  if (kCausal) {
+    const CtaCoord c = decode_cta(blockIdx.x, n_kblocks, p.b * p.h);
+    n_blk = c.x;
+    bidb = c.bh / p.h;
+    bidh = c.bh - bidb * p.h;
+  } else {
+    bidb = blockIdx.z, bidh = blockIdx.y, n_blk = blockIdx.x;
+  }
   const SeqInfo seq(p.cu_seqlens_q, p.cu_seqlens_k, bidb);
   const int k0 = n_blk * kBN;
 #ifdef FA_BWD_TRACE
@@ -121,7 +131,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
   if (k0 >= seq.seqlen_k) return;   // CTA-uniform: no key rows to produce
   const uint32_t bh = bidb * p.h + bidh;
 #ifdef FA_BWD_TRACE
-  const bool trace_cta = blockIdx.x == 1 && blockIdx.y == 0 && blockIdx.z == 0;
+  const bool trace_cta = n_blk == 1 && bidh == 0 && bidb == 0;
 #endif
 
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
@@ -765,9 +775,10 @@ cudaError_t launch_bwd_variant(const BwdTensorMaps& maps, const fa_params& p, co
   constexpr int smem = BwdSmem<DPAD>::kDynamicBytes;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
-  const dim3 grid((p.max_seqlen_k + kBN - 1) / kBN, p.h, p.b);
+  const int n_kblocks = (p.max_seqlen_k + kBN - 1) / kBN;
+  const dim3 grid = kCausal ? dim3(n_kblocks * p.h * p.b, 1, 1) : dim3(n_kblocks, p.h, p.b);
   void* span = timing_begin(stream);
-  kernel<<<grid, kBwdThreads, smem, stream>>>(maps, p, bm, ws);
+  kernel<<<grid, kBwdThreads, smem, stream>>>(maps, p, bm, ws, n_kblocks);
   timing_end(span, 1, stream);
   count_launch();
   return cudaGetLastError();

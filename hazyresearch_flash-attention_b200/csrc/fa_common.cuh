@@ -95,6 +95,27 @@ struct Elem<false> {
   static __device__ __forceinline__ T from_float(float x) { return __float2half_rn(x); }
 };
 
+// ------------------------------------------------------------------------------------------------
+// CTA order for causal launches.  Work per CTA varies (block x of a sequence has x+1 or nx-x units), so the launch is
+// a 1-D grid ordered "longest first" inside groups of kBhGroup (batch, head) pairs: the tail of the grid is made of
+// the lightest CTAs, while CTAs that run concurrently still come from few (batch, head) pairs and share K/V (forward)
+// or Q/dO and the dQ accumulator (backward) in L2.
+// ------------------------------------------------------------------------------------------------
+constexpr int kBhGroup = 24;
+struct CtaCoord {
+  int x, bh;   // x = rank by weight inside the sequence (0 = heaviest), bh = batch * h + head
+};
+__device__ __forceinline__ CtaCoord decode_cta(int lin, int nx, int n_bh) {
+  const int per_group = kBhGroup * nx;
+  const int group = lin / per_group;
+  const int r = lin - group * per_group;
+  const int gsize = min(kBhGroup, n_bh - group * kBhGroup);
+  CtaCoord c;
+  c.x = r / gsize;
+  c.bh = group * kBhGroup + (r - c.x * gsize);
+  return c;
+}
+
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 

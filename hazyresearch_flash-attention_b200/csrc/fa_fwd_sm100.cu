@@ -50,17 +50,24 @@ struct FwdTensorMaps {
 
 template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse>
 __global__ void __launch_bounds__(kNumThreads, 1)
-fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, const BlockMaskView bm) {
+fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, const BlockMaskView bm, const int n_mblocks) {
   using L = FwdSmem<DPAD>;
   constexpr int ST = L::kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int bidb = blockIdx.z, bidh = blockIdx.y;
+  // causal: 1-D launch, heaviest (latest) query blocks first within groups of (batch, head) pairs; else grid (block, h, b)
+  int bidb, bidh, m_block;
+  if (kCausal) {
+    const CtaCoord c = decode_cta(blockIdx.x, n_mblocks, p.b * p.h);
+    m_block = n_mblocks - 1 - c.x;
+    bidb = c.bh / p.h;
+    bidh = c.bh - bidb * p.h;
+  } else {
+    bidb = blockIdx.z, bidh = blockIdx.y, m_block = blockIdx.x;
+  }
   const SeqInfo seq(p.cu_seqlens_q, p.cu_seqlens_k, bidb);
-  // heaviest (latest) causal tiles first
-  const int m_block = kCausal ? (gridDim.x - 1 - blockIdx.x) : blockIdx.x;
   const int q0 = m_block * (kBlockM * kTilesPerCta);
   if (q0 >= seq.seqlen_q) return;   // CTA-uniform
 
@@ -448,9 +455,10 @@ cudaError_t launch_fwd_variant(const FwdTensorMaps& maps, const fa_params& p, co
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
   }
-  const dim3 grid((p.max_seqlen_q + kBlockM * kTilesPerCta - 1) / (kBlockM * kTilesPerCta), p.h, p.b);
+  const int n_mblocks = (p.max_seqlen_q + kBlockM * kTilesPerCta - 1) / (kBlockM * kTilesPerCta);
+  const dim3 grid = kCausal ? dim3(n_mblocks * p.h * p.b, 1, 1) : dim3(n_mblocks, p.h, p.b);
   void* span = timing_begin(stream);
-  kernel<<<grid, kNumThreads, smem, stream>>>(maps, p, bm);
+  kernel<<<grid, kNumThreads, smem, stream>>>(maps, p, bm, n_mblocks);
   timing_end(span, 0, stream);
   count_launch();
   return cudaGetLastError();
