@@ -268,10 +268,12 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
       }
     } else if (warp == 12) {
       // ===================================== MMA issuer ========================================
-      // All 32 lanes run the control flow (waits, loop counters, descriptor arithmetic stay warp-uniform, so the
-      // compiler keeps them on the uniform datapath); only the elected lane issues tcgen05.mma / tcgen05.commit.
-      if (n_iter > 0) {
-        const bool leader = lane == 0;
+      // One elected lane runs the whole role.  (Guarding each tcgen05.mma with `lane == 0` inside warp-wide control flow
+      // makes the compiler wrap every single instruction in an ELECT / BRA.U.ANY loop -- a dependent chain of ~100 clk
+      // per MMA, i.e. the issue rate, not the tensor pipe, bounded the kernel.  Inside an elect.sync region the
+      // instructions are emitted back to back from uniform registers.)
+      if (n_iter > 0 && elect_one()) {
+        constexpr bool leader = true;
         const uint32_t idesc_st = make_idesc_f16(kBf16, 128, 128, false, false);    // S^T, dP^T
         const uint32_t idesc_kv = make_idesc_f16(kBf16, 128, DPAD, false, true);    // dV, dK (B = dO / Q, MN-major)
         const uint32_t idesc_dq = make_idesc_f16(kBf16, 128, DPAD, true, true);     // dQ (A = dS^T read MN-major)
@@ -330,10 +332,8 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
         auto commit = [&](uint64_t* bar) {
           if (leader) umma_commit(bar);
         };
-        // non-blocking poll, decided by lane 0 so that the warp's control flow stays uniform
-        auto poll0 = [&](uint64_t* bar, uint32_t parity) -> bool {
-          return __shfl_sync(0xffffffffu, mbar_test_wait(bar, parity) ? 1 : 0, 0) != 0;
-        };
+        // non-blocking poll
+        auto poll0 = [&](uint64_t* bar, uint32_t parity) -> bool { return mbar_test_wait(bar, parity); };
 
         mbar_wait(k_full, 0);
         mbar_wait(&q_full[0], 0);
@@ -402,8 +402,8 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
           }
         }
         commit(dkv_full);
-        __syncwarp();
       }
+      __syncwarp();
     }
   } else if (warp >= 8) {
     // ===================================== dQ drain warps ======================================

@@ -116,6 +116,12 @@ FA_DEVICE void bulk_reduce_add_f32(void* gdst, const void* smem_src, uint32_t by
       ::"l"(reinterpret_cast<uint64_t>(gdst)), "r"(smem_u32(smem_src)), "r"(bytes)
       : "memory");
 }
+// 16-byte vector reduction into global memory (REDG.E.ADD.F32x4): no return value, registers are free at issue.
+FA_DEVICE void red_add_v4_f32(float* gptr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};\n"
+               :: "l"(gptr), "f"(__uint_as_float(a)), "f"(__uint_as_float(b)), "f"(__uint_as_float(c)), "f"(__uint_as_float(d))
+               : "memory");
+}
 FA_DEVICE void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;\n" ::: "memory"); }
 template <int N>
 FA_DEVICE void bulk_wait_group_read() { asm volatile("cp.async.bulk.wait_group.read %0;\n" ::"n"(N) : "memory"); }

@@ -10,12 +10,15 @@ using namespace fa;
 constexpr int kSub = 16384;
 
 // variant: 0 SS K/K   1 SS K/MN   2 SS MN/MN   3 TS ./MN   4 TS ./K   5 SS K/K N=256   6 bwd mix (S,dP,dV,dK,dQ)  7 SS K/K N=64
-__global__ void __launch_bounds__(256, 1) mma_bench_kernel(int variant, int reps, int traffic_warps, int random_data, long long* out) {   // random_data: bit0 random operands, bit1 TMEM-load traffic, bit2 + TMEM stores
+__global__ void __launch_bounds__(256, 1) mma_bench_kernel(int variant, int reps, int traffic_warps, int random_data, long long* out, int kind, float* scratch) {
+  // random_data: bit0 random operands, bit1 TMEM-load traffic, bit2 + TMEM stores.  kind (when bit1 clear): 0 st.shared, 3 bulk loads
+  // global->smem, 4 bulk fp32 reductions smem->global, 5 MUFU.EX2, 6 ld.shared, 7 deep tcgen05.ld (4 x 32 columns in flight)
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   __shared__ uint64_t bar;
   __shared__ uint32_t tmem_ptr;
   __shared__ int stop_flag;
+  __shared__ uint64_t tbar[8];
   const int warp = threadIdx.x >> 5;
   // zero operands (4 tiles of 32 KB)
   for (int i = threadIdx.x; i < 4 * 32768 / 4; i += blockDim.x) {
@@ -27,6 +30,7 @@ __global__ void __launch_bounds__(256, 1) mma_bench_kernel(int variant, int reps
   }
   if (threadIdx.x == 0) {
     mbar_init(&bar, 1);
+    for (int i = 0; i < 8; ++i) mbar_init(&tbar[i], 1);
     fence_mbar_init();
     stop_flag = 0;
   }
@@ -111,6 +115,66 @@ __global__ void __launch_bounds__(256, 1) mma_bench_kernel(int variant, int reps
         tmem_wait_ld();
         if (random_data & 4) { tmem_st32(t + 32, r); tmem_wait_st(); }
       }
+    } else if (kind == 3) {
+      // bulk loads global -> shared (8 KB each, private 8 KB slot per warp), like the Q / dO tile loads
+      uint8_t* slot = smem + 131072 + (warp - 1) * 2048;
+      const uint8_t* src = reinterpret_cast<const uint8_t*>(scratch) + (size_t)blockIdx.x * 65536 + (warp - 1) * 8192;
+      uint32_t ph = 0;
+      while (*sf == 0) {
+        if ((threadIdx.x & 31) == 0) {
+          mbar_arrive_expect_tx(&tbar[warp], 2048);
+          bulk_load_1d(slot, src, 2048, &tbar[warp]);
+          mbar_wait(&tbar[warp], ph);
+        }
+        ph ^= 1;
+        __syncwarp();
+      }
+    } else if (kind == 4) {
+      // bulk fp32 reductions shared -> global (2 KB each), like the dQ drain
+      uint8_t* slot = smem + 131072 + (warp - 1) * 2048;
+      float* dst = scratch + (size_t)blockIdx.x * 16384 + (warp - 1) * 2048;
+      int n = 0;
+      while (*sf == 0) {
+        if ((threadIdx.x & 31) == 0) {
+          bulk_reduce_add_f32(dst + (n & 3) * 512, slot, 2048);
+          bulk_commit_group();
+          bulk_wait_group_read<2>();
+        }
+        ++n;
+        __syncwarp();
+      }
+      if ((threadIdx.x & 31) == 0) bulk_wait_group<0>();
+    } else if (kind == 5) {
+      float x = threadIdx.x * 1e-3f, acc = 0.f;
+      while (*sf == 0) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) acc += ex2(x + i * 1e-4f);
+        x += 1e-5f;
+      }
+      if (acc == 1234.5f) out[1] = 1;
+    } else if (kind == 6) {
+      const uint32_t srcs = a0 + 131072 + (threadIdx.x & 1023) * 16;
+      uint32_t acc = 0;
+      while (*sf == 0) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          uint32_t x, y, z, w;
+          asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];\n" : "=r"(x), "=r"(y), "=r"(z), "=r"(w) : "r"(srcs));
+          acc += x + y + z + w;
+        }
+      }
+      if (acc == 0x12345u) out[1] = 1;
+    } else if (kind == 7) {
+      const uint32_t t = tm + (static_cast<uint32_t>((warp & 3) * 32) << 16) + 256;
+      uint32_t r0[32], r1[32], r2[32], r3[32];
+      uint32_t acc = 0;
+      while (*sf == 0) {
+        tmem_ld32(t, r0); tmem_ld32(t + 32, r1); tmem_ld32(t + 64, r2); tmem_ld32(t + 96, r3);
+        tmem_wait_ld();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) acc += r0[i] ^ r1[i] ^ r2[i] ^ r3[i];
+      }
+      if (acc == 0x12345u) out[1] = 1;
     } else
     while (*sf == 0) {
 #pragma unroll
@@ -128,21 +192,26 @@ __global__ void __launch_bounds__(256, 1) mma_bench_kernel(int variant, int reps
 
 int main() {
   long long* out;
-  cudaMalloc(&out, 8);
+  cudaMalloc(&out, 16);
   const int smem = 4 * 32768 + 16384 + 1024;
   cudaFuncSetAttribute(mma_bench_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   const char* names[] = {"SS K/K N128", "SS K/MN N128", "SS MN/MN N128", "TS ./MN N128", "TS ./K N128", "SS K/K N256", "bwd mix (5 tiles)", "SS K/K N64"};
   const int reps = 200;
-  for (int traffic : {8, 12, 8 + 16 + 4, 8 + 16 + 7, 8 + 16 + 32 + 4, 8 + 16 + 32 + 7}) {   // bit 3: random operand data; low bits: store-traffic warps
-    for (int v = 0; v < 8; ++v) {
-      mma_bench_kernel<<<148, 256, smem>>>(v, reps, traffic & 7, traffic >> 3, out);
+  float* scratch;
+  cudaMalloc(&scratch, (size_t)148 * 65536 * 4);
+  cudaMemset(scratch, 0, (size_t)148 * 65536 * 4);
+  const char* kinds[] = {"st.shared", "tmem ld", "tmem ld+st", "bulk load", "bulk reduce", "MUFU.EX2", "ld.shared", "deep tmem ld"};
+  struct Cfg { int warps, random, kind; };
+  const Cfg cfgs[] = {{0, 1, 0}, {7, 1, 0}, {7, 3, 1}, {7, 7, 2}, {4, 1, 3}, {7, 1, 3}, {4, 1, 4}, {7, 1, 4}, {7, 1, 5}, {7, 1, 6}, {4, 1, 7}, {7, 1, 7}};
+  for (const Cfg& c : cfgs) {
+    for (int v : {0, 2, 3, 6}) {
+      mma_bench_kernel<<<148, 256, smem>>>(v, reps, c.warps, c.random, out, c.kind, scratch);
       cudaError_t e = cudaDeviceSynchronize();
       if (e != cudaSuccess) { printf("variant %d failed: %s\n", v, cudaGetErrorString(e)); return 1; }
       long long cyc;
       cudaMemcpy(&cyc, out, 8, cudaMemcpyDeviceToHost);
       const int n_instr = reps * 8 * (v == 6 ? 5 : 1);
-      printf("cfg=%2d (random=%d, traffic warps=%d)  %-18s  %8.1f clk / MMA instr  (%.0f clk per 128x128x128 tile)\n", traffic, traffic >> 3, traffic & 7, names[v],
-             (double)cyc / n_instr, (double)cyc / n_instr * 8);
+      printf("traffic: %d warps of %-12s  %-18s  %8.1f clk / MMA instr\n", c.warps, c.warps ? kinds[c.kind] : "-", names[v], (double)cyc / n_instr);
     }
   }
   return 0;
