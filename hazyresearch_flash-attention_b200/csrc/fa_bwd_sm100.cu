@@ -30,8 +30,8 @@ namespace {
 constexpr int kBM = 128;            // queries per tile
 constexpr int kBN = 128;            // keys per CTA
 constexpr int kBwdThreads = 512;
-constexpr int kComputeRegs = 176;
-constexpr int kDrainRegs = 104;
+constexpr int kComputeRegs = 168;
+constexpr int kDrainRegs = 120;
 constexpr int kOtherRegs = 56;
 constexpr int kMaxSparseTiles = 512;
 
@@ -279,25 +279,25 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
         const uint32_t idesc_dq = make_idesc_f16(kBf16, 128, DPAD, true, true);     // dQ (A = dS^T read MN-major)
         const uint32_t aQ = smem_u32(sQ);
         const uint32_t tS = tmem_base + kColS, tDP = tmem_base + kColDP, tDV = tmem_base + kColDV, tDK = tmem_base + kColDK;
-        // descriptor bases; a byte offset o inside a tile is added as (o >> 4) to the low word
-        const uint64_t dK_k = make_smem_desc_sw128(smem_u32(sK), 16, 1024);          // K-major view (SBO = 8 rows)
-        const uint64_t dV_k = make_smem_desc_sw128(smem_u32(sV), 16, 1024);
-        const uint64_t dQ_k = make_smem_desc_sw128(aQ, 16, 1024);
-        const uint64_t dDo_k = make_smem_desc_sw128(smem_u32(sDo), 16, 1024);
-        const uint64_t dDs_k = make_smem_desc_sw128(smem_u32(sDs), 16, 1024);
-        const uint64_t dK_mn = make_smem_desc_sw128(smem_u32(sK), L::kSub, 1024);    // MN-major view (LBO = next 64 columns)
-        const uint64_t dQ_mn = make_smem_desc_sw128(aQ, L::kSub, 1024);
-        const uint64_t dDo_mn = make_smem_desc_sw128(smem_u32(sDo), L::kSub, 1024);
-        const uint64_t dDs_mn = make_smem_desc_sw128(smem_u32(sDs), L::kSub, 1024);
+        // descriptor bases (low words; the high word is constant); a byte offset o inside a tile is added as (o >> 4)
+        const uint32_t dK_k = make_smem_desc_lo(smem_u32(sK), 16);          // K-major view (SBO = 8 rows)
+        const uint32_t dV_k = make_smem_desc_lo(smem_u32(sV), 16);
+        const uint32_t dQ_k = make_smem_desc_lo(aQ, 16);
+        const uint32_t dDo_k = make_smem_desc_lo(smem_u32(sDo), 16);
+        const uint32_t dDs_k = make_smem_desc_lo(smem_u32(sDs), 16);
+        const uint32_t dK_mn = make_smem_desc_lo(smem_u32(sK), L::kSub);    // MN-major view (LBO = next 64 columns)
+        const uint32_t dQ_mn = make_smem_desc_lo(aQ, L::kSub);
+        const uint32_t dDo_mn = make_smem_desc_lo(smem_u32(sDo), L::kSub);
+        const uint32_t dDs_mn = make_smem_desc_lo(smem_u32(sDs), L::kSub);
         constexpr uint32_t kQStage = L::kTile >> 4;   // descriptor units between the two Q stages
 
         // D[keys x queries] = A[keys x d] B[queries x d]^T, both K-major
-        auto issue_t = [&](uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc) {
+        auto issue_t = [&](uint32_t d_tmem, uint32_t a_desc, uint32_t b_desc) {
           if (leader) {
 #pragma unroll
             for (int kk = 0; kk < DPAD / 16; ++kk) {
               const uint32_t off = ((kk >> 2) * L::kSub + (kk & 3) * 32) >> 4;
-              umma_ss(d_tmem, a_desc + off, b_desc + off, idesc_st, kk > 0 ? 1u : 0u);
+              umma_ss_lo(d_tmem, a_desc + off, b_desc + off, idesc_st, kk > 0 ? 1u : 0u);
             }
           }
         };
@@ -307,7 +307,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
 #pragma unroll
             for (int kk = 0; kk < kBM / 16; ++kk) {
               const uint32_t a_col = (kk < 4) ? kk * 8 : 64 + (kk - 4) * 8;   // warpgroup 1's half lives at column 64
-              umma_ts(tDV, tS + a_col, dDo_mn + (kk * 2048 >> 4), idesc_kv, (acc || kk > 0) ? 1u : 0u);
+              umma_ts_lo(tDV, tS + a_col, dDo_mn + (kk * 2048 >> 4), idesc_kv, (acc || kk > 0) ? 1u : 0u);
             }
           }
         };
@@ -317,7 +317,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
 #pragma unroll
             for (int kk = 0; kk < kBM / 16; ++kk) {
               const uint32_t off = ((kk >> 2) * L::kSub + (kk & 3) * 32) >> 4;
-              umma_ss(tDK, dDs_k + off, dQ_mn + (q_stage * kQStage + (kk * 2048 >> 4)), idesc_kv, (acc || kk > 0) ? 1u : 0u);
+              umma_ss_lo(tDK, dDs_k + off, dQ_mn + (q_stage * kQStage + (kk * 2048 >> 4)), idesc_kv, (acc || kk > 0) ? 1u : 0u);
             }
           }
         };
@@ -326,7 +326,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
           if (leader) {
 #pragma unroll
             for (int kk = 0; kk < kBN / 16; ++kk)
-              umma_ss(tDP, dDs_mn + (kk * 2048 >> 4), dK_mn + (kk * 2048 >> 4), idesc_dq, kk > 0 ? 1u : 0u);
+              umma_ss_lo(tDP, dDs_mn + (kk * 2048 >> 4), dK_mn + (kk * 2048 >> 4), idesc_dq, kk > 0 ? 1u : 0u);
           }
         };
         auto commit = [&](uint64_t* bar) {
@@ -416,7 +416,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     uint8_t* stage_gen = sDq + wq * (L::kDqBufs * 2048);
     const uint32_t stage = smem_u32(stage_gen);
     constexpr int kChunks = DPAD / 16;
-    constexpr int kRing = kChunks < 4 ? kChunks : 4;
+    constexpr int kRing = kChunks < 6 ? kChunks : 6;
     uint32_t n_issued = 0;
     for (int it = 0; it < n_iter; ++it) {
       const int m = tile_of(it);

@@ -175,6 +175,33 @@ FA_DEVICE void umma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32
       : "memory");
 }
 
+// Same, with the descriptors given as their LOW words only: for 128-byte-swizzled tiles with SBO = 1024 the high word
+// is the constant 0x40004040 (SBO >> 4 | version 1 | swizzle mode 2), so a kernel that addresses many sub-tiles
+// only carries 32-bit values around (low word = address >> 4 | (LBO >> 4) << 16; offsets add to the address field).
+constexpr uint32_t kDescHiSw128Sbo1024 = 0x40004040u;
+FA_DEVICE uint32_t make_smem_desc_lo(uint32_t saddr, uint32_t lbo_bytes) {
+  return ((saddr & 0x3FFFFu) >> 4) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
+}
+FA_DEVICE void umma_ss_lo(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "mov.b64 da, {%1, %5};\n\t"
+      "mov.b64 db, {%2, %5};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, p;\n\t}\n"
+      ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(accumulate), "r"(kDescHiSw128Sbo1024)
+      : "memory");
+}
+FA_DEVICE void umma_ts_lo(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_lo, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 db;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "mov.b64 db, {%2, %5};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], db, %3, p;\n\t}\n"
+      ::"r"(d_tmem), "r"(a_tmem), "r"(b_lo), "r"(idesc), "r"(accumulate), "r"(kDescHiSw128Sbo1024)
+      : "memory");
+}
+
 // Instruction descriptor for kind::f16 (bit layout: sm_100 UMMA "InstrDescriptor"):
 //  [4,6) D format (1 = f32) | [7,10) A format | [10,13) B format (0 = f16, 1 = bf16)
 //  [15] A major (0 = K, 1 = MN) | [16] B major | [17,23) N>>3 | [24,29) M>>4
