@@ -24,6 +24,10 @@ constexpr int kBlockN = 128;      // keys per K/V block
 constexpr int kNumThreads = 384;  // warps 0-3: softmax tile 0, 4-7: softmax tile 1, 8: TMA, 9: MMA, 10-11: idle
 constexpr int kSoftmaxRegs = 216;
 constexpr int kOtherRegs = 72;
+// P is handed to the MMA warp in kPChunks column chunks (32 keys each): the PV MMAs of a chunk are issued while the
+// softmax warps are still computing the exponentials of the next ones, which takes most of PV off the per-tile
+// dependency chain  S -> softmax -> PV -> next S.
+constexpr int kPChunks = 4;
 constexpr float kRescaleThreshold = 8.0f;   // lazy rescale: only when the row max grows by > 2^8
 
 template <int DPAD>
@@ -35,8 +39,8 @@ struct FwdSmem {
   static constexpr int kKOff = kQOff + kTilesPerCta * kTileBytes;
   static constexpr int kVOff = kKOff + kStages * kTileBytes;
   static constexpr int kBarOff = kVOff + kStages * kTileBytes;
-  // barriers: q_full[2], s_full[2], p_full[2], o_full[2], k_full[S], k_empty[S], v_full[S], v_empty[S]
-  static constexpr int kNumBars = 8 + 4 * kStages;
+  // barriers: q_full[2], s_full[2], o_full[2], p_full[2][kPChunks], k_full[S], k_empty[S], v_full[S], v_empty[S]
+  static constexpr int kNumBars = 6 + 2 * kPChunks + 4 * kStages;
   static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
   static constexpr int kListOff = kTmemPtrOff + 16;              // blocksparse: active KV block list (int16)
   static constexpr int kMaxListEntries = 1024;
@@ -74,9 +78,9 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
   uint64_t* q_full = bars + 0;
   uint64_t* s_full = bars + 2;
-  uint64_t* p_full = bars + 4;
-  uint64_t* o_full = bars + 6;
-  uint64_t* k_full = bars + 8;
+  uint64_t* o_full = bars + 4;
+  uint64_t* p_full = bars + 6;                 // [tile][chunk]
+  uint64_t* k_full = p_full + 2 * kPChunks;
   uint64_t* k_empty = k_full + ST;
   uint64_t* v_full = k_empty + ST;
   uint64_t* v_empty = v_full + ST;
@@ -132,7 +136,7 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
     for (int t = 0; t < 2; ++t) {
       mbar_init(&q_full[t], 1);
       mbar_init(&s_full[t], 1);
-      mbar_init(&p_full[t], kBlockM);
+      for (int c = 0; c < kPChunks; ++c) mbar_init(&p_full[t * kPChunks + c], kBlockM);
       mbar_init(&o_full[t], 1);
     }
     for (int s = 0; s < ST; ++s) {
@@ -210,10 +214,11 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
           }
         };
         // O_t += P_t V : A = P_t in TMEM (16-bit packed, 8 columns per K=16), B = V tile (MN-major)
-        auto issue_pv = [&](int t, int stage, bool accumulate) {
+        auto issue_pv = [&](int t, int stage, int chunk, bool accumulate) {
           const uint32_t b0 = sV_addr + stage * L::kTileBytes;
+          constexpr int kPer = kBlockN / 16 / kPChunks;
 #pragma unroll
-          for (int kk = 0; kk < kBlockN / 16; ++kk) {
+          for (int kk = chunk * kPer; kk < (chunk + 1) * kPer; ++kk) {
             umma_ts(tmem_base + 256 + t * 128, tmem_base + t * 128 + kk * 8,
                     make_smem_desc_sw128(b0 + kk * 2048, L::kSubTileBytes, 1024), idesc_pv,
                     (accumulate || kk > 0) ? 1u : 0u);
@@ -244,9 +249,12 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
 #pragma unroll
           for (int t = 0; t < kTilesPerCta; ++t) {
             if (u < cnt[t]) {
-              mbar_wait(&p_full[t], u & 1);
-              tc_fence_after();
-              issue_pv(t, s, u > 0);
+#pragma unroll
+              for (int c = 0; c < kPChunks; ++c) {
+                mbar_wait(&p_full[t * kPChunks + c], u & 1);
+                tc_fence_after();
+                issue_pv(t, s, c, u > 0);
+              }
               if (u + 1 == cnt[t]) umma_commit(&o_full[t]);
             }
             if (u + 1 < cnt[t]) {
@@ -335,44 +343,51 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
           }
         }
       }
-      // ---- exponentials, row sum, dropout, pack to 16 bit ----
+      // ---- exponentials, row sum, dropout, pack to 16 bit: one 32-key chunk at a time, each handed over as soon as its
+      //      tcgen05.st has landed (the wait for chunk c is taken after the arithmetic of chunk c+1) ----
       const float m_use = (m == -INFINITY) ? 0.f : m;
       const float neg_ms = -m_use * scale_log2;
       float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
+      constexpr int kCw = kBlockN / kPChunks;     // keys per chunk
 #pragma unroll
-      for (int c = 0; c < kBlockN; c += 4) {
-        sv[c] = ex2(fmaf(sv[c], scale_log2, neg_ms));
-        sv[c + 1] = ex2(fmaf(sv[c + 1], scale_log2, neg_ms));
-        sv[c + 2] = ex2(fmaf(sv[c + 2], scale_log2, neg_ms));
-        sv[c + 3] = ex2(fmaf(sv[c + 3], scale_log2, neg_ms));
-        sum0 += sv[c];
-        sum1 += sv[c + 1];
-        sum2 += sv[c + 2];
-        sum3 += sv[c + 3];
-      }
-      l += (sum0 + sum1) + (sum2 + sum3);
-      if (kDropout) {
+      for (int ch = 0; ch < kPChunks; ++ch) {
 #pragma unroll
-        for (int g = 0; g < kBlockN / 8; ++g) {
-          const uint4 r = dropout_rand8(pk, bh, static_cast<uint32_t>(qi), static_cast<uint32_t>(j * (kBlockN / 8) + g));
-          const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+        for (int c = ch * kCw; c < (ch + 1) * kCw; c += 4) {
+          sv[c] = ex2(fmaf(sv[c], scale_log2, neg_ms));
+          sv[c + 1] = ex2(fmaf(sv[c + 1], scale_log2, neg_ms));
+          sv[c + 2] = ex2(fmaf(sv[c + 2], scale_log2, neg_ms));
+          sv[c + 3] = ex2(fmaf(sv[c + 3], scale_log2, neg_ms));
+          sum0 += sv[c];
+          sum1 += sv[c + 1];
+          sum2 += sv[c + 2];
+          sum3 += sv[c + 3];
+        }
+        if (kDropout) {
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            if ((w[e] & 0xFFFFu) > keep_thr) sv[g * 8 + 2 * e] = 0.f;
-            if ((w[e] >> 16) > keep_thr) sv[g * 8 + 2 * e + 1] = 0.f;
+          for (int g = ch * (kCw / 8); g < (ch + 1) * (kCw / 8); ++g) {
+            const uint4 r = dropout_rand8(pk, bh, static_cast<uint32_t>(qi), static_cast<uint32_t>(j * (kBlockN / 8) + g));
+            const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              if ((w[e] & 0xFFFFu) > keep_thr) sv[g * 8 + 2 * e] = 0.f;
+              if ((w[e] >> 16) > keep_thr) sv[g * 8 + 2 * e + 1] = 0.f;
+            }
           }
         }
-      }
+        uint32_t pp[kCw / 2];
 #pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        uint32_t pp[32];
-#pragma unroll
-        for (int c = 0; c < 32; ++c) pp[c] = pack2<kBf16>(sv[half * 64 + 2 * c], sv[half * 64 + 2 * c + 1]);
-        tmem_st32(tS + half * 32, pp);
+        for (int c = 0; c < kCw / 2; ++c) pp[c] = pack2<kBf16>(sv[ch * kCw + 2 * c], sv[ch * kCw + 2 * c + 1]);
+        if (ch > 0) {
+          tmem_wait_st();                       // chunk ch-1 has landed
+          tc_fence_before();
+          mbar_arrive(&p_full[t * kPChunks + ch - 1]);
+        }
+        tmem_st16(tS + ch * (kCw / 2), pp);
       }
+      l += (sum0 + sum1) + (sum2 + sum3);
       tmem_wait_st();
       tc_fence_before();
-      mbar_arrive(&p_full[t]);
+      mbar_arrive(&p_full[t * kPChunks + kPChunks - 1]);
     }
 
     // ---- epilogue: O = acc / l (x 1/keep), lse = m*scale + ln(l) ----
