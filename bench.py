@@ -202,21 +202,43 @@ def run_ours(args, w):
     bwd_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / args.steps
 
     # ---- end-to-end: host buffers in, host buffers out, copies inside the timed region ----
+    # The (batch x heads) units are independent, so the user-level call sequence splits the batch into chunks and
+    # overlaps the pinned-memory H2D copy of chunk i+1 and the D2H copy of chunk i-1 with the kernels of chunk i
+    # (three streams); every byte of input and output still crosses PCIe inside the timed region.
+    b_tot = w["b"]
+    n_chunks = next(c for c in (8, 4, 2, 1) if b_tot % c == 0)
+    rows = (b_tot // n_chunks) * s
+    cu_c = cu[: b_tot // n_chunks + 1].contiguous()
     qkv_h = qkv.detach().cpu().pin_memory()
     dout_h = dout.cpu().pin_memory()
     out_h = torch.empty_like(dout_h).pin_memory()
     dqkv_h = torch.empty_like(qkv_h).pin_memory()
-    qkv_d = torch.empty_like(qkv_h, device=device).requires_grad_()
-    dout_d = torch.empty_like(dout_h, device=device)
+    qkv_dc = [torch.empty_like(qkv_h[:rows], device=device).requires_grad_() for _ in range(n_chunks)]
+    dout_dc = [torch.empty_like(dout_h[:rows], device=device) for _ in range(n_chunks)]
+    s_in, s_out = torch.cuda.Stream(device), torch.cuda.Stream(device)
+    ev_in = [torch.cuda.Event() for _ in range(n_chunks)]
+    ev_done = [torch.cuda.Event() for _ in range(n_chunks)]
 
     def e2e_step():
-        with torch.no_grad():
-            qkv_d.copy_(qkv_h, non_blocking=True)
-            dout_d.copy_(dout_h, non_blocking=True)
-        o = flash_attn_unpadded_qkvpacked_func(qkv_d, cu, s, p, causal=causal)
-        g, = torch.autograd.grad(o, qkv_d, dout_d)
-        out_h.copy_(o.detach(), non_blocking=True)
-        dqkv_h.copy_(g, non_blocking=True)
+        cur = torch.cuda.current_stream(device)
+        for i in range(n_chunks):
+            with torch.cuda.stream(s_in), torch.no_grad():
+                s_in.wait_event(ev_done[i])          # the previous step is done with this chunk's device buffers
+                qkv_dc[i].copy_(qkv_h[i * rows:(i + 1) * rows], non_blocking=True)
+                dout_dc[i].copy_(dout_h[i * rows:(i + 1) * rows], non_blocking=True)
+                ev_in[i].record(s_in)
+        for i in range(n_chunks):
+            cur.wait_event(ev_in[i])
+            o = flash_attn_unpadded_qkvpacked_func(qkv_dc[i], cu_c, s, p, causal=causal)
+            g, = torch.autograd.grad(o, qkv_dc[i], dout_dc[i])
+            ev_done[i].record(cur)
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(ev_done[i])
+                out_h[i * rows:(i + 1) * rows].copy_(o.detach(), non_blocking=True)
+                dqkv_h[i * rows:(i + 1) * rows].copy_(g, non_blocking=True)
+                o.record_stream(s_out)
+                g.record_stream(s_out)
+        cur.wait_stream(s_out)
 
     e2e_steps = max(2, min(args.steps, 5))
     e2e_step()
@@ -228,6 +250,11 @@ def run_ours(args, w):
     e1.record()
     barrier()
     e2e_ms = e0.elapsed_time(e1) / e2e_steps
+    if rank == 0 and os.environ.get("FA_BENCH_CHECK_E2E"):
+        torch.cuda.synchronize()
+        ref_o, ref_g = step()
+        assert torch.equal(out_h.to(device), ref_o.detach()), "e2e output differs from the resident-input run"
+        assert torch.allclose(dqkv_h.to(device).float(), ref_g.float(), rtol=2e-2, atol=2e-2)
 
     times = torch.tensor([ms_total, e2e_ms], device=device, dtype=torch.float64)
     if dist is not None:
@@ -273,7 +300,8 @@ def run_ours(args, w):
                          "peak_source": f"{peaks['src']} {'sustained' if long_region else 'burst'} bf16 matmul",
                          "traffic": traffic},
             "e2e": {"value": world * f_step / (e2e_ms * 1e-3) / 1e12, "unit": "TFLOP/s", "ms_per_step": e2e_ms,
-                    "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": in_bytes},
+                    "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": in_bytes,
+                    "pipeline": f"{n_chunks} batch chunks; H2D, kernels and D2H on three streams"},
             "gpu_launches": int(launches), "clocks": clocks,
         }
         if world == 1 and not args.no_cpu_baseline:
