@@ -1,6 +1,6 @@
 """bench.py -- attention fwd+bwd throughput on B200 (BASELINE.json metric), one JSON line on stdout.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload d128|d64] [--sweep]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload d128|d64|bert|ring64k] [--sweep]
 
 A "step" is one forward+backward pass of the attention hot path over one synthetic batch, through the public API
 (flash_attn_unpadded_qkvpacked_func -> flash_attn_cuda -> libfa_b200.so).  N > 1: one process per GPU (torchrun),
@@ -35,6 +35,9 @@ WORKLOADS = {
     # BASELINE.json configs[0]: BERT-base non-causal S512
     "bert": dict(b=8, h=12, d=64, s=512, causal=False, p=0.0, dtype="fp16",
                  name="b8 h12 d64 S512 non-causal fp16 fwd+bwd (BASELINE configs[0])"),
+    # ONE 64K-token causal problem, sequence-sharded (zig-zag) over the GPUs with the K/V ring
+    "ring64k": dict(b=1, h=12, d=128, s=65536, causal=True, p=0.0, dtype="bf16", ring=True,
+                    name="b1 h12 d128 S65536 causal bf16 fwd+bwd, zig-zag K/V ring over the GPUs (SURVEY 8e C5)"),
 }
 
 
@@ -136,6 +139,74 @@ def run_reference(args, w):
                              "sample": sample},
             "e2e": {"value": val, "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
+
+
+def run_ring(args, w):
+    """One long causal sequence sharded over the ranks (strong scaling): flash_attn/ring_attention.py."""
+    import flash_attn_cuda
+    import torch.distributed as dist
+    from flash_attn import ring_attention as ring
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29533")
+    dist.init_process_group("nccl" if world > 1 else "gloo", rank=rank, world_size=world,
+                            **({"device_id": device} if world > 1 else {}))
+    b, h, d, s = w["b"], w["h"], w["d"], w["s"]
+    c = s // (2 * world)
+    g = torch.Generator(device=device).manual_seed(99 + rank)
+    q, k, v = [torch.randn(2, b, c, h, d, device=device, dtype=torch.bfloat16, generator=g).requires_grad_() for _ in range(3)]
+    dout = torch.randn(2, b, c, h, d, device=device, dtype=torch.bfloat16, generator=g)
+
+    def step():
+        out = ring.ring_flash_attn_func(q, k, v)
+        return torch.autograd.grad(out, (q, k, v), dout)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    launches0 = flash_attn_cuda._lib.fa_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    launches = flash_attn_cuda._lib.fa_launch_count() - launches0
+    clocks = sampler.stop() if sampler else None
+    t = torch.tensor([e0.elapsed_time(e1)], device=device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = t.item() / args.steps
+    f_step = 3.5 * flops_fwd(b, h, s, s, d, True)
+    if rank == 0:
+        peaks = load_peaks()
+        value = f_step / (ms_step * 1e-3) / 1e12
+        kv_bytes = 2 * 2 * b * c * h * d * 2
+        print(json.dumps({
+            "metric": "attn fwd+bwd TFLOP/s (aggregate)", "value": value, "unit": "TFLOP/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": w["name"], "global_batch": b, "seq_len": s,
+                       "parallelism": f"sequence sharded zig-zag over {world} GPU(s); K/V (+ fp32 dK/dV in the backward) "
+                                      f"blocks rotate rank->rank+1 with NCCL P2P on a side stream",
+                       "kv_block_bytes_per_hop": kv_bytes, "per_gpu_tflops": value / world,
+                       "frac_of_bf16_peak_per_gpu": value / world / peaks["burst"],
+                       "l2": "per-GPU inputs exceed L2 at every N <= 8 (no flush needed)"},
+            "gpu_launches": int(launches), "clocks": clocks}), flush=True)
+    dist.destroy_process_group()
 
 
 def run_ours(args, w):
@@ -382,6 +453,8 @@ def main():
         run_reference(args, w)
     elif args.sweep:
         run_sweep(args)
+    elif w.get("ring"):
+        run_ring(args, w)
     else:
         run_ours(args, w)
 
