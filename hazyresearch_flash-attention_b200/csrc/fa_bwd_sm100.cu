@@ -30,8 +30,8 @@ namespace {
 constexpr int kBM = 128;            // queries per tile
 constexpr int kBN = 128;            // keys per CTA
 constexpr int kBwdThreads = 512;
-constexpr int kComputeRegs = 168;
-constexpr int kDrainRegs = 120;
+constexpr int kComputeRegs = 160;
+constexpr int kDrainRegs = 136;
 constexpr int kOtherRegs = 56;
 constexpr int kMaxSparseTiles = 512;
 
@@ -376,12 +376,6 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
             // issue whichever becomes ready first, then the other.
             bool dv_done = false, dp_done = false;
             while (!(dv_done && dp_done)) {
-              if (!dv_done && (dp_done ? (mbar_wait(p_full, (it + 1) & 1), true) : poll0(p_full, (it + 1) & 1))) {
-                FA_TRACE(2);
-                tc_fence_after();
-                issue_dv(true);
-                dv_done = true;
-              }
               if (!dp_done && (dv_done ? (mbar_wait(dq_empty, it & 1), true) : poll0(dq_empty, it & 1))) {
                 FA_TRACE(3);
                 tc_fence_after();
@@ -389,6 +383,12 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
                 commit(dp_full);
                 dp_done = true;
                 FA_TRACE(4);
+              }
+              if (!dv_done && (dp_done ? (mbar_wait(p_full, (it + 1) & 1), true) : poll0(p_full, (it + 1) & 1))) {
+                FA_TRACE(2);
+                tc_fence_after();
+                issue_dv(true);
+                dv_done = true;
               }
             }
             commit(do_empty);
@@ -410,13 +410,13 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     // Each warp drains its own 32 query rows: TMEM -> registers (up to kRing 16-column chunks in flight, so the
     // TMEM columns are handed back to the MMA warp long before the last chunk reaches global memory) -> a private
     // ring of 2 KB staging buffers -> one 2 KB cp.reduce.async.bulk per chunk.  No CTA-wide barrier is involved.
-    setmaxnreg_dec<kDrainRegs>();
+    if constexpr (kDrainRegs > 128) setmaxnreg_inc<kDrainRegs>(); else setmaxnreg_dec<kDrainRegs>();   // 128 at launch
     const int wq = warp & 3;
     const uint32_t tDQ = tmem_base + (static_cast<uint32_t>(wq * 32) << 16) + kColDP;
     uint8_t* stage_gen = sDq + wq * (L::kDqBufs * 2048);
     const uint32_t stage = smem_u32(stage_gen);
     constexpr int kChunks = DPAD / 16;
-    constexpr int kRing = kChunks < 6 ? kChunks : 6;
+    constexpr int kRing = kChunks < 8 ? kChunks : 8;
     uint32_t n_issued = 0;
     for (int it = 0; it < n_iter; ++it) {
       const int m = tile_of(it);
