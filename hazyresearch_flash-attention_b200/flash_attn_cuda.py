@@ -174,6 +174,33 @@ def _fill_common(P, q, k, v, cu_seqlens_q, cu_seqlens_k, b, h, d, total_q, total
     P.impl = _impl
 
 
+class _DeviceGuard:
+    """`with torch.cuda.device(dev)` costs ~15 us of Python per call; the common case (tensor on the current device) needs
+    no switch at all (at::cuda::CUDAGuard, fmha_api.cpp:184, is likewise a no-op then)."""
+    __slots__ = ("idx", "prev")
+
+    def __init__(self, device):
+        self.idx = device.index
+        self.prev = -1
+
+    def __enter__(self):
+        cur = torch._C._cuda_getDevice()
+        if self.idx is not None and self.idx != cur:
+            self.prev = cur
+            torch._C._cuda_setDevice(self.idx)
+        elif self.idx is None:
+            self.idx = cur
+        return self
+
+    def __exit__(self, *exc):
+        if self.prev >= 0:
+            torch._C._cuda_setDevice(self.prev)
+        return False
+
+    def raw_stream(self):
+        return torch._C._cuda_getCurrentRawStream(self.idx)   # at::cuda::getCurrentCUDAStream(), fmha_api.cpp:132
+
+
 def _workspace(P, op, device):
     nbytes = int(_lib.fa_workspace_bytes(ctypes.byref(P), op))
     if nbytes == 0:
@@ -190,7 +217,7 @@ def _fwd_impl(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, p
     P = FaParams()
     _fill_common(P, q, k, v, cu_seqlens_q, cu_seqlens_k, b, h, d, total_q, total_k, int(max_seqlen_q),
                  int(max_seqlen_k), float(p_dropout), float(softmax_scale), is_causal)
-    with torch.cuda.device(q.device):
+    with _DeviceGuard(q.device) as guard:
         o = torch.empty((total_q, h, d), dtype=q.dtype, device=q.device)
         lse = torch.empty((b, h, P.seqlen_q_rounded), dtype=torch.float32, device=q.device)
         s = None
@@ -212,11 +239,10 @@ def _fwd_impl(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, p
             op = FA_OP_FWD_BLOCK
         ws = _workspace(P, op, q.device)
         P.philox_seed, P.philox_offset = _philox_state(p_dropout, gen, q.device, P)
-        stream = torch.cuda.current_stream().cuda_stream
+        # the workspace is allocated and consumed on the current stream: the caching allocator's same-stream reuse
+        # rule already orders any later owner after this kernel
         fn = _lib.fa_fwd if blockmask is None else _lib.fa_fwd_block
-        _raise_if_failed(fn(ctypes.byref(P), stream), "flash_attn_cuda.fwd")
-        if ws is not None:
-            ws.record_stream(torch.cuda.current_stream())
+        _raise_if_failed(fn(ctypes.byref(P), guard.raw_stream()), "flash_attn_cuda.fwd")
     return [o, lse] + ([s] if return_softmax else [])
 
 
@@ -238,7 +264,7 @@ def _bwd_impl(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seql
     _fill_common(P, q, k, v, cu_seqlens_q, cu_seqlens_k, b, h, d, total_q, total_k, int(max_seqlen_q),
                  int(max_seqlen_k), float(p_dropout), float(softmax_scale), is_causal)
     _check(tuple(softmax_lse.shape) == (b, h, P.seqlen_q_rounded), "softmax_lse has the wrong shape")
-    with torch.cuda.device(q.device):
+    with _DeviceGuard(q.device) as guard:
         softmax_d = torch.empty((b, h, P.seqlen_q_rounded), dtype=torch.float32, device=q.device)
         if zero_tensors:
             dq.zero_(), dk.zero_(), dv.zero_(), softmax_d.zero_()
@@ -255,11 +281,8 @@ def _bwd_impl(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seql
             op = FA_OP_BWD_BLOCK
         ws = _workspace(P, op, q.device)
         P.philox_seed, P.philox_offset = _philox_state(p_dropout, gen, q.device, P)
-        stream = torch.cuda.current_stream().cuda_stream
         fn = _lib.fa_bwd if blockmask is None else _lib.fa_bwd_block
-        _raise_if_failed(fn(ctypes.byref(P), stream), "flash_attn_cuda.bwd")
-        if ws is not None:
-            ws.record_stream(torch.cuda.current_stream())
+        _raise_if_failed(fn(ctypes.byref(P), guard.raw_stream()), "flash_attn_cuda.bwd")
     return softmax_d
 
 
