@@ -101,7 +101,7 @@ __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t
 template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, const BlockMaskView bm, const BwdWs ws,
-                 const int n_kblocks) {
+                 const int n_kblocks, const PhiloxKey pk) {   // round keys precomputed on the host (constant bank)
   using L = BwdSmem<DPAD>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -484,8 +484,8 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     const uint32_t tDP = tmem_base + lane_base + kColDP + g * 64;
     const float scale_log2 = p.softmax_scale * kLog2e;
     const float rp_dropout = 1.f / (1.f - p.p_dropout);
-    const PhiloxKey pk = make_philox_key(p.philox_seed, p.philox_offset);
     const uint32_t keep_thr = keep_threshold_u16(p.p_dropout);
+    const uint32_t keep_thr_hi = (keep_thr << 16) | 0xFFFFu;
     const uint32_t ds_row = smem_u32(sDs) + g * L::kSub + kl * 128;
 
     for (int it = 0; it < n_iter; ++it) {
@@ -496,36 +496,31 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
 
       uint64_t keepbits = ~0ull;
       if (kDropout) {
-        // all 256 compute threads build the tile's keep bits: word (w, q) = 32 keys k0+32w.. of query row q
-        uint32_t* mbuf = sMask + (it & 1) * 512;
+        // all 256 compute threads build the tile's keep bits.  One Philox call covers 8 keys of ONE query, while a
+        // thread of the transposed tile needs 64 queries of ONE key: a warp takes 32 consecutive queries of the same
+        // key group, and a ballot per key turns its 32 answers into the word (key row, query quarter) directly.
+        uint32_t* mbuf = sMask + (it & 1) * 512;          // [128 key rows][4 query quarters]
 #pragma unroll
         for (int rep = 0; rep < 2; ++rep) {
           const int idx = threadIdx.x + rep * 256;
-          const int ql = idx & 127, w = idx >> 7;
-          uint32_t word = 0;
+          const int ql = idx & 127, w = idx >> 7;         // w (key quarter) and ql >> 5 are warp-uniform
+          uint32_t mine = 0;
 #pragma unroll
           for (int kg = 0; kg < 4; ++kg) {
             const uint4 r = dropout_rand8(pk, bh, static_cast<uint32_t>(m * kBM + ql), static_cast<uint32_t>((k0 >> 3) + w * 4 + kg));
             const uint32_t rw[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-              word |= ((rw[e] & 0xFFFFu) <= keep_thr ? 1u : 0u) << (kg * 8 + 2 * e);
-              word |= ((rw[e] >> 16) <= keep_thr ? 1u : 0u) << (kg * 8 + 2 * e + 1);
+              const uint32_t b_lo = __ballot_sync(0xffffffffu, (rw[e] & 0xFFFFu) <= keep_thr);
+              const uint32_t b_hi = __ballot_sync(0xffffffffu, rw[e] <= keep_thr_hi);
+              if (lane == kg * 8 + 2 * e) mine = b_lo;
+              if (lane == kg * 8 + 2 * e + 1) mine = b_hi;
             }
           }
-          mbuf[w * 128 + ql] = word;
+          mbuf[(w * 32 + lane) * 4 + (ql >> 5)] = mine;
         }
         named_bar_sync(1, 256);
-        const uint32_t* mrow = mbuf + wq * 128 + g * 64;
-        keepbits = 0;
-#pragma unroll
-        for (int c4 = 0; c4 < 16; ++c4) {
-          const uint4 w4 = *reinterpret_cast<const uint4*>(mrow + c4 * 4);
-          keepbits |= static_cast<uint64_t>((w4.x >> lane) & 1u) << (c4 * 4);
-          keepbits |= static_cast<uint64_t>((w4.y >> lane) & 1u) << (c4 * 4 + 1);
-          keepbits |= static_cast<uint64_t>((w4.z >> lane) & 1u) << (c4 * 4 + 2);
-          keepbits |= static_cast<uint64_t>((w4.w >> lane) & 1u) << (c4 * 4 + 3);
-        }
+        keepbits = *reinterpret_cast<const uint64_t*>(mbuf + kl * 4 + g * 2);
       }
 
       // column validity of (this key, query column c): key padding, causal diagonal, blocksparse row groups
@@ -778,7 +773,7 @@ cudaError_t launch_bwd_variant(const BwdTensorMaps& maps, const fa_params& p, co
   const int n_kblocks = (p.max_seqlen_k + kBN - 1) / kBN;
   const dim3 grid = kCausal ? dim3(n_kblocks * p.h * p.b, 1, 1) : dim3(n_kblocks, p.h, p.b);
   void* span = timing_begin(stream);
-  kernel<<<grid, kBwdThreads, smem, stream>>>(maps, p, bm, ws, n_kblocks);
+  kernel<<<grid, kBwdThreads, smem, stream>>>(maps, p, bm, ws, n_kblocks, make_philox_key(p.philox_seed, p.philox_offset));
   timing_end(span, 1, stream);
   count_launch();
   return cudaGetLastError();

@@ -22,41 +22,41 @@ namespace fa {
 // Forward, backward and the S_dmask debug kernel therefore agree for any tiling.
 // ------------------------------------------------------------------------------------------------
 struct PhiloxKey {
-  uint32_t k0, k1, c3;
+  uint32_t rk0[7], rk1[7];   // the seven round keys (key + r * Weyl constant): CTA-uniform, computed once, so the
+  uint32_t c3;               // per-call cost is 2 wide multiplies + 2 three-input XORs per round and nothing else
 };
 
 FA_HD PhiloxKey make_philox_key(uint64_t seed, uint64_t offset) {
   PhiloxKey k;
-  k.k0 = static_cast<uint32_t>(seed);
-  k.k1 = static_cast<uint32_t>(seed >> 32) ^ static_cast<uint32_t>(offset >> 32);
+  const uint32_t k0 = static_cast<uint32_t>(seed);
+  const uint32_t k1 = static_cast<uint32_t>(seed >> 32) ^ static_cast<uint32_t>(offset >> 32);
+#pragma unroll
+  for (int r = 0; r < 7; ++r) {
+    k.rk0[r] = k0 + static_cast<uint32_t>(r) * 0x9E3779B9u;
+    k.rk1[r] = k1 + static_cast<uint32_t>(r) * 0xBB67AE85u;
+  }
   k.c3 = static_cast<uint32_t>(offset);
   return k;
 }
 
-FA_HD uint32_t mulhi32(uint32_t a, uint32_t b) {
-#ifdef __CUDA_ARCH__
-  return __umulhi(a, b);
-#else
-  return static_cast<uint32_t>((static_cast<uint64_t>(a) * b) >> 32);
-#endif
-}
-
-FA_HD uint4 philox4x32_7(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
-  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+FA_HD uint4 philox4x32_7(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, const PhiloxKey& key) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
 #pragma unroll
   for (int r = 0; r < 7; ++r) {
-    const uint32_t hi0 = mulhi32(M0, c0), lo0 = M0 * c0;
-    const uint32_t hi1 = mulhi32(M1, c2), lo1 = M1 * c2;
-    const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
-    c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
-    k0 += W0; k1 += W1;
+    const uint64_t p0 = static_cast<uint64_t>(M0) * c0, p1 = static_cast<uint64_t>(M1) * c2;
+    const uint32_t n0 = static_cast<uint32_t>(p1 >> 32) ^ c1 ^ key.rk0[r];
+    const uint32_t n2 = static_cast<uint32_t>(p0 >> 32) ^ c3 ^ key.rk1[r];
+    c1 = static_cast<uint32_t>(p1);
+    c3 = static_cast<uint32_t>(p0);
+    c0 = n0;
+    c2 = n2;
   }
   return make_uint4(c0, c1, c2, c3);
 }
 
 // 8 uniforms (16 bit each) for keys 8*kgroup .. 8*kgroup+7 of query row qrow.
 FA_HD uint4 dropout_rand8(const PhiloxKey& key, uint32_t bh, uint32_t qrow, uint32_t kgroup) {
-  return philox4x32_7(qrow, kgroup, bh, key.c3, key.k0, key.k1);
+  return philox4x32_7(qrow, kgroup, bh, key.c3, key);
 }
 FA_HD uint32_t rand8_get(const uint4& r, int e) {   // e in [0, 8)
   const uint32_t w = (e >> 1) == 0 ? r.x : (e >> 1) == 1 ? r.y : (e >> 1) == 2 ? r.z : r.w;

@@ -54,7 +54,8 @@ struct FwdTensorMaps {
 
 template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse>
 __global__ void __launch_bounds__(kNumThreads, 1)
-fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, const BlockMaskView bm, const int n_mblocks) {
+fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, const BlockMaskView bm, const int n_mblocks,
+                 const PhiloxKey pk) {   // round keys precomputed on the host: they are read straight from the constant bank
   using L = FwdSmem<DPAD>;
   constexpr int ST = L::kStages;
   extern __shared__ uint8_t smem_raw[];
@@ -284,8 +285,8 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
     const uint32_t tO = tmem_base + lane_base + 256 + t * 128;
     const float scale_log2 = p.softmax_scale * kLog2e;
     const uint32_t bh = bidb * p.h + bidh;
-    const PhiloxKey pk = make_philox_key(p.philox_seed, p.philox_offset);
     const uint32_t keep_thr = keep_threshold_u16(p.p_dropout);
+    const uint32_t keep_thr_hi = (keep_thr << 16) | 0xFFFFu;
 
     float m = -INFINITY, l = 0.f;
     const int my_cnt = cnt[t];
@@ -370,7 +371,7 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
               if ((w[e] & 0xFFFFu) > keep_thr) sv[g * 8 + 2 * e] = 0.f;
-              if ((w[e] >> 16) > keep_thr) sv[g * 8 + 2 * e + 1] = 0.f;
+              if (w[e] > keep_thr_hi) sv[g * 8 + 2 * e + 1] = 0.f;      // (w >> 16) > thr without the shift
             }
           }
         }
@@ -473,7 +474,7 @@ cudaError_t launch_fwd_variant(const FwdTensorMaps& maps, const fa_params& p, co
   const int n_mblocks = (p.max_seqlen_q + kBlockM * kTilesPerCta - 1) / (kBlockM * kTilesPerCta);
   const dim3 grid = kCausal ? dim3(n_mblocks * p.h * p.b, 1, 1) : dim3(n_mblocks, p.h, p.b);
   void* span = timing_begin(stream);
-  kernel<<<grid, kNumThreads, smem, stream>>>(maps, p, bm, n_mblocks);
+  kernel<<<grid, kNumThreads, smem, stream>>>(maps, p, bm, n_mblocks, make_philox_key(p.philox_seed, p.philox_offset));
   timing_end(span, 0, stream);
   count_launch();
   return cudaGetLastError();
