@@ -190,6 +190,48 @@ __global__ void __launch_bounds__(256) merge_partials_kernel(float* __restrict__
   if (c8 == 0) lse_out[ia] = ln;   // separate buffer: the other threads of this (row, head) still read lse_acc
 }
 
+// Rotary position embedding applied to the first `n_rot` parts (q, k) of a packed (rows, n_parts, h, d) tensor in ONE
+// pass (the reference does it in pure PyTorch: flash_attn/rotary.py:21-42 -- two elementwise products, a rotate_half
+// copy and an add per tensor -- followed by a torch.stack copy of q, k, v, flash_attn/flash_attention.py:105-110).
+// Interleaved pairs: (x0, x1) -> (x0 cos - x1 sin, x1 cos + x0 sin); `sign` = -1 applies the transpose (backward).
+// cos / sin: fp32 (seqlen, d/2), position = row % seqlen.  Parts >= n_rot are copied when in != out.  fp32 math, one
+// rounding.  HBM-bound: 16-byte vectors, grid-stride over (row, part, head, 8-element group).
+template <bool kBf16>
+__global__ void __launch_bounds__(256) rotary_qk_kernel(const void* __restrict__ in_, void* __restrict__ out_, const float* __restrict__ cos_t,
+                                                        const float* __restrict__ sin_t, int64_t n_rows, int seqlen, int n_parts,
+                                                        int n_rot, int h, int d, int64_t in_row_stride, int64_t out_row_stride,
+                                                        float sign) {
+  using T = typename Elem<kBf16>::T;
+  const T* in = reinterpret_cast<const T*>(in_);
+  T* out = reinterpret_cast<T*>(out_);
+  const int d8 = d >> 3;
+  const int64_t per_row = (int64_t)n_parts * h * d8;
+  const int64_t total = n_rows * per_row;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t row = idx / per_row;
+    const int r = static_cast<int>(idx - row * per_row);
+    const int c8 = r % d8;
+    const int part = r / (d8 * h);
+    const int64_t inner = (int64_t)(r / d8) * d + c8 * 8;       // (part * h + head) * d + column
+    uint4 raw = __ldg(reinterpret_cast<const uint4*>(in + row * in_row_stride + inner));
+    if (part < n_rot) {
+      const int pos = static_cast<int>(row % seqlen);
+      const float4 c = __ldg(reinterpret_cast<const float4*>(cos_t + (int64_t)pos * (d >> 1) + c8 * 4));
+      const float4 sn = __ldg(reinterpret_cast<const float4*>(sin_t + (int64_t)pos * (d >> 1) + c8 * 4));
+      const float cs[4] = {c.x, c.y, c.z, c.w};
+      const float ss[4] = {sn.x * sign, sn.y * sign, sn.z * sign, sn.w * sign};
+      T* e = reinterpret_cast<T*>(&raw);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float x0 = Elem<kBf16>::to_float(e[2 * j]), x1 = Elem<kBf16>::to_float(e[2 * j + 1]);
+        e[2 * j] = Elem<kBf16>::from_float(x0 * cs[j] - x1 * ss[j]);
+        e[2 * j + 1] = Elem<kBf16>::from_float(x1 * cs[j] + x0 * ss[j]);
+      }
+    }
+    *reinterpret_cast<uint4*>(out + row * out_row_stride + inner) = raw;
+  }
+}
+
 template <bool kGather>
 int move_rows(void* dst, const void* src, const int64_t* indices, int64_t n, int64_t row_bytes, void* stream) {
   if (n < 0 || row_bytes < 0) return fail(FA_ERR_INVALID_ARGUMENT, "negative size");
@@ -414,6 +456,38 @@ int fa_gather_rows(void* dst, const void* src, const int64_t* indices, int64_t n
 int fa_scatter_rows(void* dst, const void* src, const int64_t* indices, int64_t n_indices, int64_t row_bytes, void* stream) {
   fa::g_last_error[0] = 0;
   return fa::move_rows<false>(dst, src, indices, n_indices, row_bytes, stream);
+}
+
+int fa_rotary_qk(const void* in, void* out, const float* cos_t, const float* sin_t, int64_t n_rows, int32_t seqlen, int32_t n_parts,
+                 int32_t n_rot, int32_t h, int32_t d, int64_t in_row_stride, int64_t out_row_stride, int32_t conjugate,
+                 int32_t is_bf16, void* stream) {
+  fa::g_last_error[0] = 0;
+  if (n_rows < 0 || seqlen <= 0 || n_parts <= 0 || n_rot < 0 || n_rot > n_parts || h <= 0 || d <= 0 || d % 8 != 0)
+    return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_rotary_qk: bad sizes (rows %lld, seqlen %d, parts %d/%d, h %d, d %d)",
+                    (long long)n_rows, seqlen, n_rot, n_parts, h, d);
+  if (n_rows == 0) return FA_OK;
+  if (!in || !out || !cos_t || !sin_t) return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_rotary_qk: NULL pointer");
+  const int64_t row_elems = (int64_t)n_parts * h * d;
+  if (in_row_stride < row_elems || out_row_stride < row_elems || in_row_stride % 8 != 0 || out_row_stride % 8 != 0)
+    return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_rotary_qk: row strides must be >= parts*h*d and multiples of 8 elements");
+  if (!fa::aligned16(in) || !fa::aligned16(out) || !fa::aligned16(cos_t) || !fa::aligned16(sin_t))
+    return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_rotary_qk: pointers must be 16-byte aligned");
+  int rc = fa::check_device();
+  if (rc != FA_OK) return rc;
+  // in place: only the rotated parts are touched
+  const int parts = (in == out) ? n_rot : n_parts;
+  if (parts == 0) return FA_OK;
+  const int64_t total = n_rows * parts * h * (d / 8);
+  const int64_t want = (total + 255) / 256;
+  const unsigned grid = static_cast<unsigned>(want < 148 * 16 ? want : 148 * 16);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const float sign = conjugate ? -1.f : 1.f;
+  if (is_bf16) fa::rotary_qk_kernel<true><<<grid, 256, 0, st>>>(in, out, cos_t, sin_t, n_rows, seqlen, parts, n_rot, h, d, in_row_stride, out_row_stride, sign);
+  else fa::rotary_qk_kernel<false><<<grid, 256, 0, st>>>(in, out, cos_t, sin_t, n_rows, seqlen, parts, n_rot, h, d, in_row_stride, out_row_stride, sign);
+  fa::count_launch();
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fa::cuda_fail(e, "rotary_qk launch");
+  return FA_OK;
 }
 
 void fa_dropout_keep8_host(uint64_t seed, uint64_t offset, uint32_t bh, uint32_t qrow, uint32_t kgroup, float p_dropout,

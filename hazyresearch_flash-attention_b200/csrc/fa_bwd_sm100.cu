@@ -101,7 +101,7 @@ __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t
 template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, const BlockMaskView bm, const BwdWs ws,
-                 const int n_kblocks, const PhiloxKey pk) {   // round keys precomputed on the host (constant bank)
+                 const int n_kblocks, const int bh_group, const PhiloxKey pk) {   // round keys precomputed on the host (constant bank)
   using L = BwdSmem<DPAD>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -110,7 +110,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
   // causal: 1-D launch, longest (lowest key block) first within groups of (batch, head) pairs; else grid (block, h, b)
   int bidb, bidh, n_blk;
   if (kCausal) {
-    const CtaCoord c = decode_cta(blockIdx.x, n_kblocks, p.b * p.h);
+    const CtaCoord c = decode_cta(blockIdx.x, n_kblocks, p.b * p.h, bh_group);
     n_blk = c.x;
     bidb = c.bh / p.h;
     bidh = c.bh - bidb * p.h;
@@ -772,8 +772,10 @@ cudaError_t launch_bwd_variant(const BwdTensorMaps& maps, const fa_params& p, co
   if (e != cudaSuccess) return e;
   const int n_kblocks = (p.max_seqlen_k + kBN - 1) / kBN;
   const dim3 grid = kCausal ? dim3(n_kblocks * p.h * p.b, 1, 1) : dim3(n_kblocks, p.h, p.b);
+  // per (batch, head) pair a causal group streams Q, dO (16 bit) and the fp32 dQ accumulator
+  const int bh_group = causal_bh_group((uint64_t)ws.sq_pad * DPAD * 8);
   void* span = timing_begin(stream);
-  kernel<<<grid, kBwdThreads, smem, stream>>>(maps, p, bm, ws, n_kblocks, make_philox_key(p.philox_seed, p.philox_offset));
+  kernel<<<grid, kBwdThreads, smem, stream>>>(maps, p, bm, ws, n_kblocks, bh_group, make_philox_key(p.philox_seed, p.philox_offset));
   timing_end(span, 1, stream);
   count_launch();
   return cudaGetLastError();

@@ -5,6 +5,7 @@
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../../include/fa_b200.h"
 
@@ -97,23 +98,34 @@ struct Elem<false> {
 
 // ------------------------------------------------------------------------------------------------
 // CTA order for causal launches.  Work per CTA varies (block x of a sequence has x+1 or nx-x units), so the launch is
-// a 1-D grid ordered "longest first" inside groups of kBhGroup (batch, head) pairs: the tail of the grid is made of
+// a 1-D grid ordered "longest first" inside groups of `bh_group` (batch, head) pairs: the tail of the grid is made of
 // the lightest CTAs, while CTAs that run concurrently still come from few (batch, head) pairs and share K/V (forward)
 // or Q/dO and the dQ accumulator (backward) in L2.
 // ------------------------------------------------------------------------------------------------
-constexpr int kBhGroup = 24;
+constexpr int kBhGroupMax = 24;
 struct CtaCoord {
   int x, bh;   // x = rank by weight inside the sequence (0 = heaviest), bh = batch * h + head
 };
-__device__ __forceinline__ CtaCoord decode_cta(int lin, int nx, int n_bh) {
-  const int per_group = kBhGroup * nx;
+__device__ __forceinline__ CtaCoord decode_cta(int lin, int nx, int n_bh, int bh_group) {
+  const int per_group = bh_group * nx;
   const int group = lin / per_group;
   const int r = lin - group * per_group;
-  const int gsize = min(kBhGroup, n_bh - group * kBhGroup);
+  const int gsize = min(bh_group, n_bh - group * bh_group);
   CtaCoord c;
   c.x = r / gsize;
-  c.bh = group * kBhGroup + (r - c.x * gsize);
+  c.bh = group * bh_group + (r - c.x * gsize);
   return c;
+}
+// Group size: as many (batch, head) pairs as keep the concurrently streamed tensors of a group (`bytes_per_pair`:
+// K and V in the forward; Q, dO and the fp32 dQ accumulator in the backward) inside ~3/4 of the 126 MB L2, at most 24.
+// FA_BH_GROUP overrides it (experiments).
+inline int causal_bh_group(uint64_t bytes_per_pair) {
+  const char* e = getenv("FA_BH_GROUP");
+  const int forced = e != nullptr ? atoi(e) : 0;
+  if (forced > 0) return forced;
+  const uint64_t budget = 96ull << 20;
+  const uint64_t g = bytes_per_pair > 0 ? budget / bytes_per_pair : kBhGroupMax;
+  return static_cast<int>(g < 1 ? 1 : (g > kBhGroupMax ? kBhGroupMax : g));
 }
 
 constexpr float kLog2e = 1.4426950408889634f;

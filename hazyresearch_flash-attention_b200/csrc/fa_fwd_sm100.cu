@@ -55,7 +55,7 @@ struct FwdTensorMaps {
 template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse>
 __global__ void __launch_bounds__(kNumThreads, 1)
 fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, const BlockMaskView bm, const int n_mblocks,
-                 const PhiloxKey pk) {   // round keys precomputed on the host: they are read straight from the constant bank
+                 const int bh_group, const PhiloxKey pk) {   // round keys precomputed on the host: they are read straight from the constant bank
   using L = FwdSmem<DPAD>;
   constexpr int ST = L::kStages;
   extern __shared__ uint8_t smem_raw[];
@@ -65,7 +65,7 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
   // causal: 1-D launch, heaviest (latest) query blocks first within groups of (batch, head) pairs; else grid (block, h, b)
   int bidb, bidh, m_block;
   if (kCausal) {
-    const CtaCoord c = decode_cta(blockIdx.x, n_mblocks, p.b * p.h);
+    const CtaCoord c = decode_cta(blockIdx.x, n_mblocks, p.b * p.h, bh_group);
     m_block = n_mblocks - 1 - c.x;
     bidb = c.bh / p.h;
     bidh = c.bh - bidb * p.h;
@@ -473,8 +473,10 @@ cudaError_t launch_fwd_variant(const FwdTensorMaps& maps, const fa_params& p, co
   }
   const int n_mblocks = (p.max_seqlen_q + kBlockM * kTilesPerCta - 1) / (kBlockM * kTilesPerCta);
   const dim3 grid = kCausal ? dim3(n_mblocks * p.h * p.b, 1, 1) : dim3(n_mblocks, p.h, p.b);
+  // per (batch, head) pair a causal group streams K and V
+  const int bh_group = causal_bh_group((uint64_t)p.max_seqlen_k * DPAD * 4);
   void* span = timing_begin(stream);
-  kernel<<<grid, kNumThreads, smem, stream>>>(maps, p, bm, n_mblocks, make_philox_key(p.philox_seed, p.philox_offset));
+  kernel<<<grid, kNumThreads, smem, stream>>>(maps, p, bm, n_mblocks, bh_group, make_philox_key(p.philox_seed, p.philox_offset));
   timing_end(span, 0, stream);
   count_launch();
   return cudaGetLastError();

@@ -10,7 +10,7 @@ import torch.nn as nn
 
 from flash_attn.bert_padding import pad_input, unpad_input
 from flash_attn.flash_attn_interface import flash_attn_unpadded_qkvpacked_func
-from flash_attn.rotary import RotaryEmbedding, RotaryEmbedding2D
+from flash_attn.rotary import RotaryEmbedding, RotaryEmbedding2D, apply_rotary_qkvpacked_, rotary_tables
 
 
 class FlashAttention(nn.Module):
@@ -72,6 +72,7 @@ class FlashMHA(nn.Module):
             self.rotary_emb = RotaryEmbedding(self.head_dim)
         elif self.use_rotary_emb == '2d':
             self.rotary_emb = RotaryEmbedding2D(self.head_dim)
+        self._rotary_cache = (None, None)   # ((seqlen, device), (cos, sin)) for the fused rotary kernel
         self.Wqkv = nn.Linear(embed_dim, 3 * embed_dim, bias=bias, **factory_kwargs)
         self.inner_attn = FlashAttention(attention_dropout=attention_dropout, **factory_kwargs)
         self.out_proj = nn.Linear(embed_dim, embed_dim, bias=bias, **factory_kwargs)
@@ -79,11 +80,15 @@ class FlashMHA(nn.Module):
     def forward(self, x, key_padding_mask=None, need_weights=False):
         """x: (batch, seqlen, embed_dim); key_padding_mask: bool (batch, seqlen).  Returns (out, None)."""
         b, s, _ = x.shape
-        qkv = self.Wqkv(x).reshape(b, s, 3, self.num_heads, self.head_dim)
+        qkv = self.Wqkv(x)
         if self.use_rotary_emb:
-            query, key, value = qkv.unbind(dim=2)
-            query, key = self.rotary_emb(query, key, seq_dimension=-3)
-            qkv = torch.stack([query, key, value], dim=2)
+            # one in-place kernel pass over q and k (the reference: elementwise torch ops + torch.stack, :105-110)
+            key = (s, qkv.device)
+            if self._rotary_cache[0] != key:
+                self._rotary_cache = (key, rotary_tables(self.use_rotary_emb, s, self.head_dim, qkv.device))
+            cos, sin = self._rotary_cache[1]
+            qkv = apply_rotary_qkvpacked_(qkv.contiguous(), cos, sin, self.num_heads)
+        qkv = qkv.reshape(b, s, 3, self.num_heads, self.head_dim)
         context, attn_weights = self.inner_attn(qkv, key_padding_mask=key_padding_mask, need_weights=need_weights,
                                                 causal=self.causal)
         return self.out_proj(context.reshape(b, s, self.embed_dim)), attn_weights

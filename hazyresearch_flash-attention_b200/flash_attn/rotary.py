@@ -1,6 +1,8 @@
 """Rotary position embeddings used by FlashMHA(use_rotary_emb=...).  Behavioural equivalent of the reference's
 pure-PyTorch flash_attn/rotary.py (interleaved pairs (x0, x1), (x2, x3), ...; tables cached per sequence length).
-Outside the attention kernel's hot path -- plain torch elementwise code, no kernels here."""
+The modules keep the reference's elementwise formulation (any device); FlashMHA goes through `apply_rotary_qkvpacked_`,
+which rotates q and k of the packed qkv tensor in place with one CUDA kernel (fa_rotary_qk) instead of the reference's
+elementwise passes + torch.stack copy (flash_attention.py:105-110)."""
 import math
 from typing import Tuple
 
@@ -80,3 +82,61 @@ class RotaryEmbedding2D(torch.nn.Module):
         if seq_dimension == -3:
             q_emb, k_emb = q_emb.transpose(1, 2), k_emb.transpose(1, 2)
         return q_emb, k_emb
+
+
+# ---------------------------------------------------------------------------------------------------
+# fused path used by FlashMHA
+# ---------------------------------------------------------------------------------------------------
+def rotary_tables(mode, seqlen, head_dim, device):
+    """fp32 (seqlen, head_dim/2) cos / sin tables: entry [s, j] is the angle applied to the pair (2j, 2j+1) of a head at
+    sequence position s.  '1d': s * 10000^(-2j/d) (reference rotary.py:68, 84-88).  '2d' (square grids, rotary.py:103-135):
+    pairs of the first half of the head rotate with the grid column s % side, pairs of the second half with the grid row
+    s // side, both with the frequencies of a (d/2)-dimensional 1-D embedding."""
+    pos = torch.arange(seqlen, device=device, dtype=torch.float32)
+    if mode == '1d':
+        inv_freq = 1.0 / (10000 ** (torch.arange(0, head_dim, 2, device=device).float() / head_dim))
+        freqs = torch.outer(pos, inv_freq)
+    else:
+        assert mode == '2d' and head_dim % 4 == 0
+        side = int(math.sqrt(seqlen))
+        assert seqlen == side ** 2
+        half = head_dim // 2
+        inv_freq = 1.0 / (10000 ** (torch.arange(0, half, 2, device=device).float() / half))
+        idx = torch.arange(seqlen, device=device)
+        freqs = torch.cat([torch.outer((idx % side).float(), inv_freq),
+                           torch.outer(torch.div(idx, side, rounding_mode='floor').float(), inv_freq)], dim=-1)
+    return torch.cos(freqs).contiguous(), torch.sin(freqs).contiguous()
+
+
+class _RotaryQKVPackedInplace(torch.autograd.Function):
+    """qkv (b, s, 3*h*d): q and k rotated IN PLACE (the input is the fresh output of the Wqkv projection, whose backward
+    does not need it); the backward applies the transposed rotation to the q and k parts of the incoming gradient."""
+
+    @staticmethod
+    def forward(ctx, qkv, cos, sin, nheads):
+        import flash_attn_cuda
+        b, s, w = qkv.shape
+        flat = qkv.view(b * s, 3, nheads, w // (3 * nheads))
+        flash_attn_cuda.rotary_qk(flat, flat, cos, sin, s, n_rot=2)
+        ctx.mark_dirty(qkv)
+        ctx.save_for_backward(cos, sin)
+        ctx.nheads = nheads
+        return qkv
+
+    @staticmethod
+    def backward(ctx, dqkv):
+        import flash_attn_cuda
+        cos, sin = ctx.saved_tensors
+        dqkv = dqkv.contiguous()
+        b, s, w = dqkv.shape
+        shape = (b * s, 3, ctx.nheads, w // (3 * ctx.nheads))
+        out = torch.empty_like(dqkv)
+        flash_attn_cuda.rotary_qk(dqkv.view(shape), out.view(shape), cos, sin, s, n_rot=2, conjugate=True)
+        return out, None, None, None
+
+
+def apply_rotary_qkvpacked_(qkv, cos, sin, nheads):
+    """In-place rotary of q and k inside the contiguous (b, s, 3*h*d) output of a QKV projection (columns ordered
+    (three, h, d) as in flash_attention.py:105-106); returns the same tensor."""
+    assert qkv.dim() == 3 and qkv.is_contiguous() and qkv.shape[-1] % (3 * nheads) == 0
+    return _RotaryQKVPackedInplace.apply(qkv, cos, sin, nheads)

@@ -72,6 +72,9 @@ def _load_library():
                        ctypes.c_void_p]
     lib.fa_merge_partials.restype = ctypes.c_int
     lib.fa_merge_partials.argtypes = [ctypes.c_void_p] * 5 + [ctypes.c_int32] * 8 + [ctypes.c_void_p]
+    lib.fa_rotary_qk.restype = ctypes.c_int
+    lib.fa_rotary_qk.argtypes = ([ctypes.c_void_p] * 4 + [ctypes.c_int64] + [ctypes.c_int32] * 5 + [ctypes.c_int64] * 2
+                                 + [ctypes.c_int32] * 2 + [ctypes.c_void_p])
     lib.fa_dropout_keep8_host.restype = None
     lib.fa_dropout_keep8_host.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint32,
                                           ctypes.c_uint32, ctypes.c_float, ctypes.c_void_p]
@@ -378,6 +381,27 @@ def merge_partials(o_acc, lse_acc, lse_out, o_blk, lse_blk, batch, seqlen, first
                                     lse_acc.shape[2], lse_blk.shape[2], 1 if o_blk.dtype == torch.bfloat16 else 0,
                                     1 if first else 0, torch.cuda.current_stream().cuda_stream)
     _raise_if_failed(rc, "fa_merge_partials")
+
+
+def rotary_qk(qkv_in, qkv_out, cos, sin, seqlen, n_rot=2, conjugate=False):
+    """Rotary embedding of the first n_rot parts of a packed (rows, n_parts, h, d) tensor (fa_rotary_qk).
+    qkv_out may be qkv_in (in place: only the rotated parts are touched); cos / sin are fp32 (seqlen, d/2)."""
+    _check(qkv_in.is_cuda and qkv_in.dim() == 4 and qkv_in.dtype in (torch.float16, torch.bfloat16),
+           "qkv must be a (rows, parts, h, d) fp16/bf16 CUDA tensor")
+    _check(qkv_out.shape == qkv_in.shape and qkv_out.dtype == qkv_in.dtype and qkv_out.device == qkv_in.device,
+           "output must match the input")
+    rows, n_parts, h, d = qkv_in.shape
+    for t in (qkv_in, qkv_out):
+        _check(t.stride(3) == 1 and t.stride(2) == d and t.stride(1) == h * d, "(parts, h, d) must be contiguous within a row")
+    for t in (cos, sin):
+        _check(t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and tuple(t.shape) == (seqlen, d // 2),
+               "cos / sin must be contiguous fp32 (seqlen, d/2)")
+    with torch.cuda.device(qkv_in.device):
+        rc = _lib.fa_rotary_qk(_ptr(qkv_in), _ptr(qkv_out), _ptr(cos), _ptr(sin), rows, seqlen, n_parts, n_rot, h, d,
+                               qkv_in.stride(0), qkv_out.stride(0), 1 if conjugate else 0,
+                               1 if qkv_in.dtype == torch.bfloat16 else 0, torch.cuda.current_stream().cuda_stream)
+    _raise_if_failed(rc, "fa_rotary_qk")
+    return qkv_out
 
 
 def kernel_timing(enable):

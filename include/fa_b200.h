@@ -10,6 +10,7 @@
  *                                               (native source absent from the reference snapshot)
  *   fa_fwd_block  <- flash_attn_cuda.fwd_block  called at flash_attn/flash_blocksparse_attn_interface.py:45-47
  *   fa_bwd_block  <- flash_attn_cuda.bwd_block  called at flash_attn/flash_blocksparse_attn_interface.py:56-58
+ *   fa_rotary_qk  <- apply_rotary_pos_emb       flash_attn/rotary.py:31-42 as used by FlashMHA (flash_attention.py:105-110)
  *   fa_gather_rows / fa_scatter_rows            the torch.gather / scatter_ / index_put the reference issues in
  *                                               flash_attn/bert_padding.py:21-22, 30-35, 48-53, 59
  *
@@ -138,6 +139,16 @@ int fa_scatter_rows(void* dst, const void* src, const int64_t* indices, int64_t 
 int fa_merge_partials(float* o_acc, const float* lse_acc, float* lse_out, const void* o_blk, const float* lse_blk, int32_t b,
                       int32_t h, int32_t d, int32_t seqlen, int32_t lse_acc_stride, int32_t lse_blk_stride, int32_t is_bf16,
                       int32_t first, void* stream);
+
+/* Rotary position embedding of the first n_rot parts (q, k) of a packed (n_rows, n_parts, h, d) 16-bit tensor in one
+ * pass -- replaces the pure-PyTorch apply_rotary_pos_emb + torch.stack the reference runs before attention in FlashMHA
+ * (flash_attn/rotary.py:21-42, flash_attn/flash_attention.py:105-110).  Interleaved pairs:
+ *   (x0, x1) -> (x0 cos - x1 sin, x1 cos + x0 sin);  conjugate != 0 applies the transpose (the backward).
+ * cos_t / sin_t: fp32 (seqlen, d/2); position of a row = row % seqlen.  Row strides in elements.  in == out rotates in
+ * place; otherwise parts >= n_rot (v) are copied. */
+int fa_rotary_qk(const void* in, void* out, const float* cos_t, const float* sin_t, int64_t n_rows, int32_t seqlen,
+                 int32_t n_parts, int32_t n_rot, int32_t h, int32_t d, int64_t in_row_stride, int64_t out_row_stride,
+                 int32_t conjugate, int32_t is_bf16, void* stream);
 
 /* Host-only helper exposing the dropout RNG for tests: fills keep[8] (0/1) for the 8 key positions
  * 8*kgroup .. 8*kgroup+7 of query row `qrow` in (batch*h + head) = bh.  Pure CPU code. */

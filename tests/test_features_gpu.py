@@ -311,6 +311,53 @@ def test_flash_mha_module(rotary):
     assert torch.isfinite(x.grad).all() and x.grad.abs().max().item() > 0
 
 
+@pytest.mark.parametrize("mode", ["1d", "2d"])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("d", [32, 64, 128])
+def test_fused_rotary_kernel_matches_reference_modules(mode, dtype, d):
+    """fa_rotary_qk (in place, and its transposed backward) against the reference's elementwise formulation
+    (flash_attn/rotary.py) evaluated in fp32; tolerance: the reference's own rule, error <= 2x the error of the
+    16-bit PyTorch path."""
+    from flash_attn.rotary import RotaryEmbedding, RotaryEmbedding2D, apply_rotary_qkvpacked_, rotary_tables
+    b, s, h = 3, 144, 5
+    torch.manual_seed(0)
+    qkv = torch.randn(b, s, 3, h, d, device=DEV, dtype=dtype)
+    mod = (RotaryEmbedding(d) if mode == "1d" else RotaryEmbedding2D(d)).to(DEV)
+    q32, k32 = mod(qkv[:, :, 0].float(), qkv[:, :, 1].float(), seq_dimension=-3)
+    q16, k16 = mod(qkv[:, :, 0], qkv[:, :, 1], seq_dimension=-3)
+    cos, sin = rotary_tables(mode, s, d, DEV)
+    x = qkv.reshape(b, s, -1).clone().requires_grad_()
+    y = apply_rotary_qkvpacked_(x * 1.0, cos, sin, h)       # x * 1.0: a fresh non-leaf tensor, as in FlashMHA
+    y5 = y.reshape(b, s, 3, h, d)
+    assert torch.equal(y5[:, :, 2], qkv[:, :, 2])                               # v untouched
+    for got, ref, pt in ((y5[:, :, 0], q32, q16), (y5[:, :, 1], k32, k16)):
+        assert orc.max_abs_err(got, ref) <= 2 * orc.max_abs_err(pt, ref) + 1e-6
+    # backward = transposed rotation of the q, k parts, identity on v
+    g = torch.randn_like(y)
+    (gx,) = torch.autograd.grad(y, x, g)
+    xr = qkv.float().clone().requires_grad_()
+    qr, kr = mod(xr[:, :, 0], xr[:, :, 1], seq_dimension=-3)
+    yr = torch.stack([qr, kr, xr[:, :, 2]], dim=2)
+    (gr,) = torch.autograd.grad(yr, xr, g.reshape(b, s, 3, h, d).float())
+    x16 = qkv.clone().requires_grad_()
+    q_, k_ = mod(x16[:, :, 0], x16[:, :, 1], seq_dimension=-3)
+    (g16,) = torch.autograd.grad(torch.stack([q_, k_, x16[:, :, 2]], dim=2), x16, g.reshape(b, s, 3, h, d))
+    assert orc.max_abs_err(gx.reshape(b, s, 3, h, d), gr) <= 2 * orc.max_abs_err(g16, gr) + 1e-6
+    assert torch.equal(gx.reshape(b, s, 3, h, d)[:, :, 2], g.reshape(b, s, 3, h, d)[:, :, 2])
+
+
+def test_fused_rotary_rejects_bad_arguments():
+    import flash_attn_cuda
+    x = torch.randn(8, 3, 2, 32, device=DEV, dtype=torch.float16)
+    cos = torch.zeros(8, 16, device=DEV)
+    with pytest.raises(RuntimeError):
+        flash_attn_cuda.rotary_qk(x, x, cos[:, :8].contiguous(), cos[:, :8].contiguous(), 8)
+    with pytest.raises(RuntimeError):
+        flash_attn_cuda.rotary_qk(x.float(), x.float(), cos, cos, 8)
+    with pytest.raises(RuntimeError):
+        flash_attn_cuda.rotary_qk(x.transpose(1, 2), x.transpose(1, 2), cos, cos, 8)
+
+
 @pytest.mark.parametrize("width", [2, 8, 64, 768, 1000])
 @pytest.mark.parametrize("dtype", [torch.float16, torch.float32])
 def test_bert_padding_kernels_match_torch(width, dtype):

@@ -130,6 +130,22 @@ def test_rotary_matches_reference():
         assert torch.allclose(got, ref, atol=1e-6, rtol=1e-6)
 
 
+def test_rotary_tables_reproduce_reference_modules():
+    """The fp32 tables the fused kernel consumes, applied with the kernel's pair formula, against the outputs the
+    reference's RotaryEmbedding / RotaryEmbedding2D produced for the same inputs (tests/golden/rotary_cases.pt)."""
+    from flash_attn.rotary import rotary_tables
+    c = U.load_golden("rotary_cases.pt")
+    for mode, names in (("1d", ("q1", "k1")), ("2d", ("q2", "k2"))):
+        for x, ref in ((c["q"], c[names[0]]), (c["k"], c[names[1]])):
+            b, s, h, d = x.shape
+            cos, sin = rotary_tables(mode, s, d, x.device)
+            assert cos.shape == (s, d // 2) and cos.dtype == torch.float32
+            x0, x1 = x.float()[..., 0::2], x.float()[..., 1::2]
+            cs, sn = cos[None, :, None, :], sin[None, :, None, :]
+            got = torch.stack((x0 * cs - x1 * sn, x1 * cs + x0 * sn), dim=-1).flatten(-2)
+            assert torch.allclose(got, ref.float(), atol=1e-5, rtol=1e-5)
+
+
 # ------------------------------------------------------------------------------------------------------------
 # C-ABI library: loads without a GPU and exports every symbol the header declares
 # ------------------------------------------------------------------------------------------------------------
@@ -144,7 +160,7 @@ def test_library_exports_every_declared_symbol():
     lib = ctypes.CDLL(LIB)
     names = _declared_symbols()
     assert {"fa_fwd", "fa_bwd", "fa_fwd_block", "fa_bwd_block", "fa_gather_rows", "fa_scatter_rows",
-            "fa_last_error", "fa_workspace_bytes", "fa_philox_increment"} <= set(names)
+            "fa_rotary_qk", "fa_last_error", "fa_workspace_bytes", "fa_philox_increment"} <= set(names)
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/fa_b200.h but not exported"
 
