@@ -768,12 +768,17 @@ cudaError_t launch_bwd_variant(const BwdTensorMaps& maps, const fa_params& p, co
                                cudaStream_t stream) {
   auto kernel = bwd_sm100_kernel<DPAD, kBf16, kCausal, kDropout, kSparse>;
   constexpr int smem = BwdSmem<DPAD>::kDynamicBytes;
-  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  if (e != cudaSuccess) return e;
+  static bool configured[16] = {};   // per device (as in the forward): the attribute call costs ~1.5 us of host time
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 16 || !configured[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    if (dev < 16) configured[dev] = true;
+  }
   const int n_kblocks = (p.max_seqlen_k + kBN - 1) / kBN;
   const dim3 grid = kCausal ? dim3(n_kblocks * p.h * p.b, 1, 1) : dim3(n_kblocks, p.h, p.b);
-  // per (batch, head) pair a causal group streams Q, dO (16 bit) and the fp32 dQ accumulator
-  const int bh_group = causal_bh_group((uint64_t)ws.sq_pad * DPAD * 8);
+  const int bh_group = causal_bh_group(p.max_seqlen_q > p.max_seqlen_k ? p.max_seqlen_q : p.max_seqlen_k);
   void* span = timing_begin(stream);
   kernel<<<grid, kBwdThreads, smem, stream>>>(maps, p, bm, ws, n_kblocks, bh_group, make_philox_key(p.philox_seed, p.philox_offset));
   timing_end(span, 1, stream);

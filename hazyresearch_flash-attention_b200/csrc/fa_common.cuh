@@ -116,16 +116,16 @@ __device__ __forceinline__ CtaCoord decode_cta(int lin, int nx, int n_bh, int bh
   c.bh = group * bh_group + (r - c.x * gsize);
   return c;
 }
-// Group size: as many (batch, head) pairs as keep the concurrently streamed tensors of a group (`bytes_per_pair`:
-// K and V in the forward; Q, dO and the fp32 dQ accumulator in the backward) inside ~3/4 of the 126 MB L2, at most 24.
-// FA_BH_GROUP overrides it (experiments).
-inline int causal_bh_group(uint64_t bytes_per_pair) {
+// Group size, measured on B200 at d = 128 (b x S = 64K tokens, h = 12; profiles/r01_bh_group_sweep.log): the best group
+// holds about 64K tokens' worth of (batch, head) pairs -- 16 pairs at S = 4096, 6-8 at 8192, 2-4 at 16384, 24-32 at
+// 2048 -- i.e. roughly 64 MB of Q + dO + fp32 dQ accumulator in the backward, half the L2.  Larger groups thrash the L2
+// (-20 % at one group for the whole batch), much smaller ones lengthen the tail.  FA_BH_GROUP overrides it (experiments).
+inline int causal_bh_group(int max_seqlen) {
   const char* e = getenv("FA_BH_GROUP");
   const int forced = e != nullptr ? atoi(e) : 0;
   if (forced > 0) return forced;
-  const uint64_t budget = 96ull << 20;
-  const uint64_t g = bytes_per_pair > 0 ? budget / bytes_per_pair : kBhGroupMax;
-  return static_cast<int>(g < 1 ? 1 : (g > kBhGroupMax ? kBhGroupMax : g));
+  const int g = 65536 / (max_seqlen > 0 ? max_seqlen : 1);
+  return g < 1 ? 1 : (g > kBhGroupMax ? kBhGroupMax : g);
 }
 
 constexpr float kLog2e = 1.4426950408889634f;

@@ -473,8 +473,7 @@ cudaError_t launch_fwd_variant(const FwdTensorMaps& maps, const fa_params& p, co
   }
   const int n_mblocks = (p.max_seqlen_q + kBlockM * kTilesPerCta - 1) / (kBlockM * kTilesPerCta);
   const dim3 grid = kCausal ? dim3(n_mblocks * p.h * p.b, 1, 1) : dim3(n_mblocks, p.h, p.b);
-  // per (batch, head) pair a causal group streams K and V
-  const int bh_group = causal_bh_group((uint64_t)p.max_seqlen_k * DPAD * 4);
+  const int bh_group = causal_bh_group(p.max_seqlen_q > p.max_seqlen_k ? p.max_seqlen_q : p.max_seqlen_k);
   void* span = timing_begin(stream);
   kernel<<<grid, kNumThreads, smem, stream>>>(maps, p, bm, n_mblocks, bh_group, make_philox_key(p.philox_seed, p.philox_offset));
   timing_end(span, 0, stream);

@@ -151,6 +151,10 @@ def _philox_state(p_dropout, gen, device, params):
     (fmha_api.cpp:228-235).  No RNG state is touched when p_dropout == 0 (fmha_api.cpp:231)."""
     if p_dropout <= 0.0:
         return 0, 0
+    # The (seed, offset) pair is read on the host: under CUDA-graph capture it would be frozen into the graph and every
+    # replay would draw the same mask (the reference's PhiloxCudaState reads a device-side offset instead, fmha.h:39).
+    _check(not torch.cuda.is_current_stream_capturing(),
+           "dropout under CUDA graph capture is not supported (capture with p_dropout = 0)")
     if gen is None:
         idx = device.index if device.index is not None else torch.cuda.current_device()
         gen = torch.cuda.default_generators[idx]

@@ -311,6 +311,42 @@ def test_flash_mha_module(rotary):
     assert torch.isfinite(x.grad).all() and x.grad.abs().max().item() > 0
 
 
+def test_cuda_graph_capture_and_replay():
+    """Forward + backward are stream-ordered with no host synchronisation (fmha_api.cpp:132), so one step can be
+    captured in a CUDA graph and replayed on new data in the same buffers; dropout under capture is refused."""
+    from flash_attn.flash_attn_interface import flash_attn_unpadded_qkvpacked_func
+    b, s, h, d = 3, 384, 4, 64
+    torch.manual_seed(0)
+    qkv = torch.randn(b * s, 3, h, d, device=DEV, dtype=torch.float16, requires_grad=True)
+    dout = torch.randn(b * s, h, d, device=DEV, dtype=torch.float16)
+    cu = torch.arange(0, (b + 1) * s, s, device=DEV, dtype=torch.int32)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for _ in range(2):
+            out = flash_attn_unpadded_qkvpacked_func(qkv, cu, s, 0.0, causal=True)
+            torch.autograd.grad(out, qkv, dout)
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        g_out = flash_attn_unpadded_qkvpacked_func(qkv, cu, s, 0.0, causal=True)
+        (g_dqkv,) = torch.autograd.grad(g_out, qkv, dout)
+    with torch.no_grad():
+        qkv.copy_(torch.randn_like(qkv))
+        dout.copy_(torch.randn_like(dout))
+    graph.replay()
+    torch.cuda.synchronize()
+    out = flash_attn_unpadded_qkvpacked_func(qkv, cu, s, 0.0, causal=True)
+    (dqkv,) = torch.autograd.grad(out, qkv, dout)
+    assert torch.equal(g_out, out)
+    assert torch.equal(g_dqkv[:, 1:], dqkv[:, 1:])                      # dK, dV: bitwise deterministic
+    assert orc.max_abs_err(g_dqkv[:, 0], dqkv[:, 0]) < 1e-2           # dQ: fp32 reduction order may differ
+    with pytest.raises(RuntimeError):
+        g2 = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g2):
+            flash_attn_unpadded_qkvpacked_func(qkv, cu, s, 0.1, causal=True)
+
+
 @pytest.mark.parametrize("mode", ["1d", "2d"])
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
 @pytest.mark.parametrize("d", [32, 64, 128])

@@ -44,10 +44,16 @@ def run(cfg, reps=10):
                 os.environ.pop(k, None)
             else:
                 os.environ[k] = v
+    try:
+        import subprocess
+        smi = subprocess.run(["nvidia-smi", "--query-gpu=clocks.sm,power.draw,temperature.gpu", "--format=csv,noheader,nounits"],
+                             capture_output=True, text=True, timeout=10).stdout.strip().replace(", ", "/")
+    except Exception:
+        smi = "?"
     f = 4.0 * b * h * s * s * d / (2 if causal else 1)
     kf, kb = kt["fwd_ms"] / kt["fwd_launches"], kt["bwd_ms"] / kt["bwd_launches"]
     print(f"{cfg}: fwd {tf/reps:.3f} ms (kernel {kf:.3f} ms, {f/kf/1e9:.0f} TF/s)  "
-          f"bwd {tb/reps:.3f} ms (kernel {kb:.3f} ms, {2.5*f/kb/1e9:.0f} TF/s)  fwd+bwd {3.5*f/((tf+tb)/reps)/1e9:.0f} TF/s", flush=True)
+          f"bwd {tb/reps:.3f} ms (kernel {kb:.3f} ms, {2.5*f/kb/1e9:.0f} TF/s)  fwd+bwd {3.5*f/((tf+tb)/reps)/1e9:.0f} TF/s  [idle-after MHz/W/C {smi}]", flush=True)
     del qkv, dout, out
     torch.cuda.empty_cache()
 
