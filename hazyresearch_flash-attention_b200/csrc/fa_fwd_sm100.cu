@@ -52,10 +52,21 @@ struct FwdTensorMaps {
   CUtensorMap q, k, v;
 };
 
+// Optional timeline tracing of one CTA (build with -DFA_BWD_TRACE, i.e. `make trace`; tools/trace_fwd.py)
+#ifdef FA_BWD_TRACE
+__device__ long long g_fwd_trace[64 * 32];
+#define FA_FTRACE(u_, slot)                                                                                \
+  do {                                                                                                     \
+    if (trace_cta && (u_) < 64 && (threadIdx.x & 31) == 0) g_fwd_trace[(u_) * 32 + (slot)] = clock64();   \
+  } while (0)
+#else
+#define FA_FTRACE(u_, slot) do { } while (0)
+#endif
+
 template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse>
 __global__ void __launch_bounds__(kNumThreads, 1)
 fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, const BlockMaskView bm, const int n_mblocks,
-                 const int bh_group, const PhiloxKey pk) {   // round keys precomputed on the host: they are read straight from the constant bank
+                 const int bh_group, const int pingpong, const PhiloxKey pk) {   // round keys precomputed on the host: they are read straight from the constant bank
   using L = FwdSmem<DPAD>;
   constexpr int ST = L::kStages;
   extern __shared__ uint8_t smem_raw[];
@@ -75,6 +86,9 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
   const SeqInfo seq(p.cu_seqlens_q, p.cu_seqlens_k, bidb);
   const int q0 = m_block * (kBlockM * kTilesPerCta);
   if (q0 >= seq.seqlen_q) return;   // CTA-uniform
+#ifdef FA_BWD_TRACE
+  const bool trace_cta = bidb == 0 && bidh == 0 && m_block == n_mblocks - 1;
+#endif
 
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
   uint64_t* q_full = bars + 0;
@@ -253,9 +267,11 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
 #pragma unroll
               for (int c = 0; c < kPChunks; ++c) {
                 mbar_wait(&p_full[t * kPChunks + c], u & 1);
+                if (c == 0) FA_FTRACE(u, 16 + 4 * t);
                 tc_fence_after();
                 issue_pv(t, s, c, u > 0);
               }
+              FA_FTRACE(u, 17 + 4 * t);
               if (u + 1 == cnt[t]) umma_commit(&o_full[t]);
             }
             if (u + 1 < cnt[t]) {
@@ -266,6 +282,7 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
               }
               issue_qk(t, s_next);
               umma_commit(&s_full[t]);
+              FA_FTRACE(u, 18 + 4 * t);
             }
           }
           umma_commit(&v_empty[s]);
@@ -290,9 +307,16 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
 
     float m = -INFINITY, l = 0.f;
     const int my_cnt = cnt[t];
+    // Ping-pong of the exponential phases: the two tiles of a CTA share the SM's 16 ex2/clk.  Left alone they drift into
+    // lockstep -- both warpgroups load S and take the row max at the same time (MUFU idle), then both exponentiate at
+    // half speed.  A turn token (named barriers 2 and 3) lets only one tile at a time into its exponential phase, so the
+    // other tile's S MMA, TMEM load and row max run underneath it.  Only over the blocks both tiles walk.
+    const int n_turns = pingpong ? min(cnt[0], cnt[1]) : 0;
+    if (t == 1 && n_turns > 0) named_bar_arrive(2, 256);      // tile 0 goes first
     for (int u = 0; u < my_cnt; ++u) {
       const int j = kSparse ? blk_list[u] : u;
       mbar_wait(&s_full[t], u & 1);
+      if ((warp & 3) == 0) FA_FTRACE(u, 8 * t + 0);
       tc_fence_after();
       float sv[kBlockN];
       {
@@ -303,6 +327,7 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
         tmem_ld32(tS + 96, r[3]);
         tmem_wait_ld();
       }
+      if ((warp & 3) == 0) FA_FTRACE(u, 8 * t + 1);
       // ---- masking: key padding, causal (top-left aligned: key <= query), blocksparse ----
       int limit = seq.seqlen_k - j * kBlockN;
       if (kCausal) limit = min(limit, qi + 1 - j * kBlockN);
@@ -348,6 +373,9 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
       //      tcgen05.st has landed (the wait for chunk c is taken after the arithmetic of chunk c+1) ----
       const float m_use = (m == -INFINITY) ? 0.f : m;
       const float neg_ms = -m_use * scale_log2;
+      if ((warp & 3) == 0) FA_FTRACE(u, 8 * t + 2);
+      if (u < n_turns) named_bar_sync(2 + t, 256);            // wait for this tile's turn on the MUFU
+      if ((warp & 3) == 0) FA_FTRACE(u, 8 * t + 3);
       float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
       constexpr int kCw = kBlockN / kPChunks;     // keys per chunk
 #pragma unroll
@@ -385,10 +413,13 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
         }
         tmem_st16(tS + ch * (kCw / 2), pp);
       }
+      if ((warp & 3) == 0) FA_FTRACE(u, 8 * t + 4);
+      if (u < n_turns && !(t == 1 && u + 1 == n_turns)) named_bar_arrive(3 - t, 256);   // hand the turn over
       l += (sum0 + sum1) + (sum2 + sum3);
       tmem_wait_st();
       tc_fence_before();
       mbar_arrive(&p_full[t * kPChunks + kPChunks - 1]);
+      if ((warp & 3) == 0) FA_FTRACE(u, 8 * t + 5);
     }
 
     // ---- epilogue: O = acc / l (x 1/keep), lse = m*scale + ln(l) ----
@@ -437,6 +468,12 @@ PFN_cuTensorMapEncodeTiled_v12000 get_tensor_map_encoder() {
 
 }  // namespace
 
+#ifdef FA_BWD_TRACE
+extern "C" __attribute__((visibility("default"))) int fa_debug_read_fwd_trace(long long* host, int n) {
+  return (int)cudaMemcpyFromSymbol(host, g_fwd_trace, sizeof(long long) * n);
+}
+#endif
+
 // (d, h, total) view of a packed (total, h, d) tensor with arbitrary row / head strides; box = 64 x 1 x rows,
 // 128-byte swizzle, out-of-bounds elements read as zero (this is what pads head dims to 64 / 128 and
 // clips the last rows of the packed batch).
@@ -474,8 +511,13 @@ cudaError_t launch_fwd_variant(const FwdTensorMaps& maps, const fa_params& p, co
   const int n_mblocks = (p.max_seqlen_q + kBlockM * kTilesPerCta - 1) / (kBlockM * kTilesPerCta);
   const dim3 grid = kCausal ? dim3(n_mblocks * p.h * p.b, 1, 1) : dim3(n_mblocks, p.h, p.b);
   const int bh_group = causal_bh_group(p.max_seqlen_q > p.max_seqlen_k ? p.max_seqlen_q : p.max_seqlen_k);
+  // exponential-phase ping-pong (see the kernel).  Measured (profiles/r01_kernel_experiments_ab.log): +10 % at d = 64,
+  // +1.5 % at d = 128 causal, -3 % at d = 128 non-causal (there the second tile fills the MUFU bubbles the first one
+  // leaves around its TMEM stores better than the turn token does), neutral with dropout (issue-bound, not MUFU-bound).
+  const char* pp_env = getenv("FA_FWD_PINGPONG");
+  const int pingpong = pp_env != nullptr ? atoi(pp_env) : ((!kDropout && (DPAD == 64 || kCausal)) ? 1 : 0);
   void* span = timing_begin(stream);
-  kernel<<<grid, kNumThreads, smem, stream>>>(maps, p, bm, n_mblocks, bh_group, make_philox_key(p.philox_seed, p.philox_offset));
+  kernel<<<grid, kNumThreads, smem, stream>>>(maps, p, bm, n_mblocks, bh_group, pingpong, make_philox_key(p.philox_seed, p.philox_offset));
   timing_end(span, 0, stream);
   count_launch();
   return cudaGetLastError();

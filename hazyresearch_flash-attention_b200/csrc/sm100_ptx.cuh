@@ -343,6 +343,9 @@ FA_DEVICE void store_acc_rows_coalesced(uint32_t taddr, bool have_acc, float sca
 FA_DEVICE void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;\n" ::"r"(id), "r"(nthreads) : "memory");
 }
+FA_DEVICE void named_bar_arrive(int id, int nthreads) {
+  asm volatile("bar.arrive %0, %1;\n" ::"r"(id), "r"(nthreads) : "memory");
+}
 template <int N>
 FA_DEVICE void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" ::"n"(N)); }
 template <int N>
