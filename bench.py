@@ -402,6 +402,7 @@ def run_sweep(args):
     device = torch.device("cuda", 0)
     peaks = load_peaks()
     pts = [("d64", dict(b=8, h=12, d=64, dtype="fp16", p=0.1), [512, 1024, 2048, 4096]),
+           ("d64_p0", dict(b=8, h=12, d=64, dtype="fp16", p=0.0), [512, 1024, 2048, 4096]),
            ("d128", dict(b=16, h=12, d=128, dtype="bf16", p=0.0), [512, 1024, 2048, 4096, 8192, 16384])]
     for tag, base, seqs in pts:
         for s in seqs:
@@ -411,28 +412,50 @@ def run_sweep(args):
                 w = dict(base, s=s, causal=causal)
                 qkv, dout, cu = make_batch(w, device, 0)
                 qkv.requires_grad_()
-                ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
-                reps = 5
-                for it in range(2):
-                    n = 2 if it == 0 else reps
-                    torch.cuda.synchronize()
-                    tf = tb = 0.0
-                    for _ in range(n):
-                        ev[0].record()
-                        out = flash_attn_unpadded_qkvpacked_func(qkv, cu, s, w["p"], causal=causal)
-                        ev[1].record()
-                        if not args.fwd_only:
-                            torch.autograd.grad(out, qkv, dout)
-                        ev[2].record()
-                        torch.cuda.synchronize()
-                        tf += ev[0].elapsed_time(ev[1])
-                        tb += ev[1].elapsed_time(ev[2])
-                tf, tb = tf / reps, max(tb / reps, 1e-9)
                 f = flops_fwd(w["b"], w["h"], s, s, w["d"], causal)
-                print(json.dumps({"sweep": tag, "seqlen": s, "causal": causal, "dropout": w["p"],
-                                  "fwd_ms": tf, "bwd_ms": tb, "fwd_tflops": f / tf / 1e9, "bwd_tflops": 2.5 * f / tb / 1e9,
-                                  "fwd_bwd_tflops": 3.5 * f / (tf + tb) / 1e9,
-                                  "frac_burst_peak": 3.5 * f / (tf + tb) / 1e9 / peaks["burst"]}), flush=True)
+
+                def fwd_only():
+                    return flash_attn_unpadded_qkvpacked_func(qkv, cu, s, w["p"], causal=causal)
+
+                def fwd_bwd():
+                    torch.autograd.grad(fwd_only(), qkv, dout)
+
+                def timed(fn, reps):
+                    """`reps` calls enqueued back to back (no host sync in between: launch latency overlaps device work)."""
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    torch.cuda.synchronize()
+                    e0.record()
+                    for _ in range(reps):
+                        fn()
+                    e1.record()
+                    torch.cuda.synchronize()
+                    return e0.elapsed_time(e1) / reps
+
+                for _ in range(3):
+                    fwd_bwd()
+                est = timed(fwd_bwd, 2)
+                reps = int(min(200, max(5, 40.0 / max(est, 1e-3))))
+                tf = timed(fwd_only, reps)
+                tfb = tf if args.fwd_only else timed(fwd_bwd, reps)
+                tb = max(tfb - tf, 1e-9)
+                row = {"sweep": tag, "seqlen": s, "causal": causal, "dropout": w["p"], "reps": reps,
+                       "fwd_ms": tf, "bwd_ms": tb, "fwd_tflops": f / tf / 1e9, "bwd_tflops": 2.5 * f / tb / 1e9,
+                       "fwd_bwd_tflops": 3.5 * f / tfb / 1e9, "frac_burst_peak": 3.5 * f / tfb / 1e9 / peaks["burst"]}
+                if w["p"] == 0.0 and not args.fwd_only:
+                    # the same step replayed from a CUDA graph (dropout cannot be captured: host-side Philox offset)
+                    side = torch.cuda.Stream()
+                    side.wait_stream(torch.cuda.current_stream())
+                    with torch.cuda.stream(side):
+                        fwd_bwd()
+                    torch.cuda.current_stream().wait_stream(side)
+                    graph = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(graph):
+                        fwd_bwd()
+                    tg = timed(graph.replay, reps)
+                    row["graph_fwd_bwd_ms"] = tg
+                    row["graph_fwd_bwd_tflops"] = 3.5 * f / tg / 1e9
+                    del graph
+                print(json.dumps(row), flush=True)
                 del qkv, dout
 
 
