@@ -364,7 +364,10 @@ def run_ours(args, w):
                        "fwd_kernel_ms": kf_ms, "bwd_kernel_ms": kb_ms,
                        "fwd_kernel_tflops": f_fwd / (kf_ms * 1e-3) / 1e12,
                        "bwd_kernel_tflops": 2.5 * f_fwd / (kb_ms * 1e-3) / 1e12,
-                       "frac_of_bf16_peak_fwd_bwd": value / world / peak},
+                       "frac_of_bf16_peak_fwd_bwd": value / world / peak,
+                       # the same number against the sustained cuBLAS rate and the nominal dense bf16 peak
+                       "frac_of_sustained_bf16": value / world / peaks["sustained"],
+                       "frac_of_nominal_2250": value / world / 2250.0},
             "roofline": {"bound": "tensor", "kernel": f"{dom}_sm100_kernel (tcgen05/TMA), algorithmic FLOPs "
                                                          f"{dom_flops / 1e12:.3f} T per launch, {dom_ms:.3f} ms per launch",
                          "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
@@ -459,6 +462,101 @@ def run_sweep(args):
                 del qkv, dout
 
 
+def _sweep_time(fwd, leaves, dout, graph_ok):
+    """fwd / fwd+bwd time of one point: calls enqueued back to back, optional CUDA-graph replay of the step."""
+    def fwd_bwd():
+        torch.autograd.grad(fwd(), leaves, dout)
+
+    def timed(fn, reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    for _ in range(3):
+        fwd_bwd()
+    reps = int(min(200, max(5, 40.0 / max(timed(fwd_bwd, 2), 1e-3))))
+    tf, tfb, tg = timed(fwd, reps), timed(fwd_bwd, reps), None
+    if graph_ok:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            fwd_bwd()
+        torch.cuda.current_stream().wait_stream(side)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            fwd_bwd()
+        tg = timed(graph.replay, reps)
+    return reps, tf, tfb, tg
+
+
+def run_sweep_extra(args):
+    """The remaining measurement inputs of SURVEY 8(d): C4 (varlen BERT batch, 32K tokens of mixed lengths 64-512,
+    d = 64 / 80 / 96, and cross-attention with independent q / k lengths) and C5's blocksparse butterfly mask."""
+    from flash_attn.flash_attn_interface import flash_attn_unpadded_kvpacked_func, flash_attn_unpadded_qkvpacked_func
+    from flash_attn.flash_blocksparse_attn_interface import convert_blockmask, flash_blocksparse_attn_func
+    from flash_attn.flash_blocksparse_attention import ButterflySparsityConfig
+    device = torch.device("cuda", 0)
+    peaks = load_peaks()
+    h = 12
+
+    def draw_lengths(seed, total=32768):
+        g = torch.Generator().manual_seed(seed)
+        out, acc = [], 0
+        while acc < total:
+            n = min(int(torch.randint(64, 513, (1,), generator=g)), total - acc)
+            out.append(n)
+            acc += n
+        return torch.tensor(out, dtype=torch.int64)
+
+    def emit(row, f, reps, tf, tfb, tg):
+        tb = max(tfb - tf, 1e-9)
+        row.update({"reps": reps, "fwd_ms": tf, "bwd_ms": tb, "fwd_tflops": f / tf / 1e9, "bwd_tflops": 2.5 * f / tb / 1e9,
+                    "fwd_bwd_tflops": 3.5 * f / tfb / 1e9, "frac_burst_peak": 3.5 * f / tfb / 1e9 / peaks["burst"]})
+        if tg is not None:
+            row.update({"graph_fwd_bwd_ms": tg, "graph_fwd_bwd_tflops": 3.5 * f / tg / 1e9})
+        print(json.dumps(row), flush=True)
+
+    lens_q, lens_k = draw_lengths(0), draw_lengths(1)
+    cu_q = torch.nn.functional.pad(lens_q.cumsum(0), (1, 0)).to(device=device, dtype=torch.int32)
+    for d in (64, 80, 96):
+        for causal in (False, True):
+            qkv = torch.randn(32768, 3, h, d, device=device, dtype=torch.float16, requires_grad=True)
+            dout = torch.randn(32768, h, d, device=device, dtype=torch.float16)
+            mx = int(lens_q.max())
+            f = 4.0 * h * d * float((lens_q * lens_q).sum()) / (2 if causal else 1)
+            r = _sweep_time(lambda: flash_attn_unpadded_qkvpacked_func(qkv, cu_q, mx, 0.0, causal=causal), qkv, dout, True)
+            emit({"sweep": "varlen32k", "d": d, "seqs": len(lens_q), "causal": causal, "dropout": 0.0}, f, *r)
+    # cross-attention: the same number of sequences, independent q / k lengths (tests/test_flash_attn.py:446-447)
+    nseq = min(len(lens_q), len(lens_k))
+    lq, lk = lens_q[:nseq], lens_k[:nseq]
+    cq = torch.nn.functional.pad(lq.cumsum(0), (1, 0)).to(device=device, dtype=torch.int32)
+    ck = torch.nn.functional.pad(lk.cumsum(0), (1, 0)).to(device=device, dtype=torch.int32)
+    for d in (64, 96):
+        q = torch.randn(int(lq.sum()), h, d, device=device, dtype=torch.float16, requires_grad=True)
+        kv = torch.randn(int(lk.sum()), 2, h, d, device=device, dtype=torch.float16, requires_grad=True)
+        dout = torch.randn_like(q)
+        f = 4.0 * h * d * float((lq * lk).sum())
+        r = _sweep_time(lambda: flash_attn_unpadded_kvpacked_func(q, kv, cq, ck, int(lq.max()), int(lk.max()), 0.0), (q, kv), dout, True)
+        emit({"sweep": "cross_varlen", "d": d, "seqs": nseq, "causal": False, "dropout": 0.0}, f, *r)
+    # blocksparse, butterfly layout at the kernel's (16 x 256) granularity, d = 64 fp16 (SURVEY 8d, C5)
+    for s, b in ((4096, 8), (16384, 2)):
+        layout = ButterflySparsityConfig().make_layout(s).to(device)
+        mask = convert_blockmask(layout, causal=False)
+        density = float(layout.float().mean())
+        qkv = torch.randn(b * s, 3, h, 64, device=device, dtype=torch.float16, requires_grad=True)
+        dout = torch.randn(b * s, h, 64, device=device, dtype=torch.float16)
+        cu = torch.arange(0, (b + 1) * s, s, device=device, dtype=torch.int32)
+        f = 4.0 * b * h * s * s * 64 * density
+        r = _sweep_time(lambda: flash_blocksparse_attn_func(qkv, cu, mask, 0.0, s, convert_mask=False), qkv, dout, True)
+        emit({"sweep": "blocksparse_butterfly", "d": 64, "seqlen": s, "b": b, "density": density, "causal": False,
+              "dropout": 0.0}, f, *r)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -476,6 +574,7 @@ def main():
         run_reference(args, w)
     elif args.sweep:
         run_sweep(args)
+        run_sweep_extra(args)
     elif w.get("ring"):
         run_ring(args, w)
     else:
