@@ -41,16 +41,19 @@ struct BwdSmem {
   static constexpr int kSub = 128 * 128;                  // [128 rows x 64 cols] swizzle-128B sub tile
   static constexpr int kKOff = 0;
   static constexpr int kVOff = kKOff + kTile;
-  static constexpr int kQOff = kVOff + kTile;             // 2 stages
-  static constexpr int kDoOff = kQOff + 2 * kTile;        // 1 stage
+  // Q stages: a Q tile lives from S(t) (issued two slots early) to dK(t), so with two stages the load of Q(t+2) sits on
+  // the per-tile critical path (dK(t) done -> TMA -> S(t+2)); d <= 64 has the shared memory for a third stage
+  static constexpr int kQStages = DPAD <= 64 ? 3 : 2;
+  static constexpr int kQOff = kVOff + kTile;
+  static constexpr int kDoOff = kQOff + kQStages * kTile;   // 1 stage
   static constexpr int kDsOff = kDoOff + kTile;           // dS^T: [128 keys x 128 queries] 16 bit
   static constexpr int kDqBufs = 3;                       // dQ staging: per drain warp a ring of 2 KB buffers
   static constexpr int kDqOff = kDsOff + 2 * kSub;
-  static constexpr int kStatOff = kDqOff + 4 * kDqBufs * 2048;   // 2 stages x { -lse*log2e [128], D [128] } fp32
-  static constexpr int kMaskOff = kStatOff + 2 * 1024;    // dropout keep bits: 2 x [4 key words][128 queries] u32
+  static constexpr int kStatOff = kDqOff + 4 * kDqBufs * 2048;   // kQStages x { -lse*log2e [128], D [128] } fp32
+  static constexpr int kMaskOff = kStatOff + kQStages * 1024;    // dropout keep bits: 2 x [4 key words][128 queries] u32
   static constexpr int kListOff = kMaskOff + 2 * 2048;    // blocksparse: int16 list[512], uint8 flags[512]
   static constexpr int kBarOff = kListOff + kMaxSparseTiles * 3;
-  static constexpr int kNumBars = 16;
+  static constexpr int kNumBars = 18;
   static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
   static constexpr int kTotal = kTmemPtrOff + 16;
   static constexpr int kDynamicBytes = kTotal + 1024;     // + alignment slack
@@ -137,18 +140,19 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
   uint64_t* k_full = bars + 0;
   uint64_t* v_full = bars + 1;
-  uint64_t* q_full = bars + 2;    // [2]
-  uint64_t* q_empty = bars + 4;   // [2]
-  uint64_t* do_full = bars + 6;
-  uint64_t* do_empty = bars + 7;
-  uint64_t* s_full = bars + 8;
-  uint64_t* dp_full = bars + 9;
-  uint64_t* p_full = bars + 10;
-  uint64_t* ds_full = bars + 11;
-  uint64_t* ds_empty = bars + 12;
-  uint64_t* dq_full = bars + 13;
-  uint64_t* dq_empty = bars + 14;
-  uint64_t* dkv_full = bars + 15;
+  constexpr int kQ = L::kQStages;
+  uint64_t* q_full = bars + 2;    // [kQ <= 3]
+  uint64_t* q_empty = bars + 5;   // [kQ <= 3]
+  uint64_t* do_full = bars + 8;
+  uint64_t* do_empty = bars + 9;
+  uint64_t* s_full = bars + 10;
+  uint64_t* dp_full = bars + 11;
+  uint64_t* p_full = bars + 12;
+  uint64_t* ds_full = bars + 13;
+  uint64_t* ds_empty = bars + 14;
+  uint64_t* dq_full = bars + 15;
+  uint64_t* dq_empty = bars + 16;
+  uint64_t* dkv_full = bars + 17;
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + L::kTmemPtrOff);
   int16_t* tile_list = reinterpret_cast<int16_t*>(smem + L::kListOff);
   uint8_t* tile_flags = smem + L::kListOff + kMaxSparseTiles * 2;
@@ -192,7 +196,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
   if (threadIdx.x == 0) {
     mbar_init(k_full, 1);
     mbar_init(v_full, 1);
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < kQ; ++s) {
       mbar_init(&q_full[s], 1);
       mbar_init(&q_empty[s], 1);
     }
@@ -228,6 +232,10 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
   uint32_t* sMask = reinterpret_cast<uint32_t*>(smem + L::kMaskOff);
 
   constexpr uint32_t kColS = 0, kColDP = 128, kColDV = 256, kColDK = 384;
+  // d <= 64 leaves TMEM columns free: dQ gets its own (448..511) instead of aliasing dP^T, which takes the
+  // dQ(t) -> drain -> dP(t+1) hop out of the per-tile dependency chain
+  constexpr bool kDqAliased = DPAD > 64;
+  constexpr uint32_t kColDQ = kDqAliased ? kColDP : 448;
 
   if (warp >= 12) {
     setmaxnreg_dec<kOtherRegs>();
@@ -248,8 +256,8 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
         }
         for (int it = 0; it < n_iter; ++it) {
           const int m = tile_of(it);
-          const int s = it & 1;
-          mbar_wait(&q_empty[s], ((it >> 1) & 1) ^ 1);
+          const int s = it % kQ;
+          mbar_wait(&q_empty[s], ((it / kQ) & 1) ^ 1);
           FA_TRACE(20);
           mbar_arrive_expect_tx(&q_full[s], L::kTile + 1024);
 #pragma unroll
@@ -326,7 +334,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
           if (leader) {
 #pragma unroll
             for (int kk = 0; kk < kBN / 16; ++kk)
-              umma_ss_lo(tDP, dDs_mn + (kk * 2048 >> 4), dK_mn + (kk * 2048 >> 4), idesc_dq, kk > 0 ? 1u : 0u);
+              umma_ss_lo(tmem_base + kColDQ, dDs_mn + (kk * 2048 >> 4), dK_mn + (kk * 2048 >> 4), idesc_dq, kk > 0 ? 1u : 0u);
           }
         };
         auto commit = [&](uint64_t* bar) {
@@ -358,10 +366,16 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
           commit(s_full);
         }
         for (int it = 0; it < n_iter; ++it) {
-          const int s = it & 1;
+          const int s = it % kQ;
           mbar_wait(ds_full, it & 1);
           FA_TRACE(0);
           tc_fence_after();
+          if constexpr (!kDqAliased) {
+            if (it > 0) {   // the dQ(it) columns only have to wait for the drain of dQ(it-1), which finished long ago
+              mbar_wait(dq_empty, (it - 1) & 1);
+              tc_fence_after();
+            }
+          }
           issue_dq();
           FA_TRACE(6);
           commit(dq_full);
@@ -374,7 +388,12 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
             mbar_wait(do_full, (it + 1) & 1);
             // dV(it+1) needs P(it+1) from the compute warps, dP(it+1) needs dQ(it) drained out of the aliased columns:
             // issue whichever becomes ready first, then the other.
-            bool dv_done = false, dp_done = false;
+            if constexpr (!kDqAliased) {   // dP(it+1): its columns are free since dS(it) exists; no drain to wait for
+              issue_t(tDP, dV_k, dDo_k);
+              commit(dp_full);
+              FA_TRACE(4);
+            }
+            bool dv_done = false, dp_done = !kDqAliased;
             while (!(dv_done && dp_done)) {
               if (!dp_done && (dv_done ? (mbar_wait(dq_empty, it & 1), true) : poll0(dq_empty, it & 1))) {
                 FA_TRACE(3);
@@ -393,9 +412,10 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
             }
             commit(do_empty);
             if (it + 2 < n_iter) {
-              mbar_wait(&q_full[s], ((it + 2) >> 1) & 1);
+              const int s2 = (it + 2) % kQ;
+              mbar_wait(&q_full[s2], ((it + 2) / kQ) & 1);
               tc_fence_after();
-              issue_t(tS, dK_k, dQ_k + s * kQStage);
+              issue_t(tS, dK_k, dQ_k + s2 * kQStage);
               commit(s_full);
               FA_TRACE(5);
             }
@@ -412,7 +432,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     // ring of 2 KB staging buffers -> one 2 KB cp.reduce.async.bulk per chunk.  No CTA-wide barrier is involved.
     if constexpr (kDrainRegs > 128) setmaxnreg_inc<kDrainRegs>(); else setmaxnreg_dec<kDrainRegs>();   // 128 at launch
     const int wq = warp & 3;
-    const uint32_t tDQ = tmem_base + (static_cast<uint32_t>(wq * 32) << 16) + kColDP;
+    const uint32_t tDQ = tmem_base + (static_cast<uint32_t>(wq * 32) << 16) + kColDQ;
     uint8_t* stage_gen = sDq + wq * (L::kDqBufs * 2048);
     const uint32_t stage = smem_u32(stage_gen);
     constexpr int kChunks = DPAD / 16;
@@ -490,7 +510,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
 
     for (int it = 0; it < n_iter; ++it) {
       const int m = tile_of(it);
-      const int s = it & 1;
+      const int s = it % kQ;
       const uint32_t nl_s = smem_u32(sStat + s * 256 + g * 64);
       const uint32_t d_s = smem_u32(sStat + s * 256 + 128 + g * 64);
 
