@@ -235,6 +235,13 @@ def run_ours(args, w):
     f_fwd = flops_fwd(w["b"], w["h"], s, s, w["d"], causal)
     f_step = 3.5 * f_fwd
     in_bytes = qkv.numel() * qkv.element_size() + dout.numel() * dout.element_size()
+    # timing rule: inputs larger than L2, or L2 flushed between timed iterations (small workloads: bert, ...)
+    flush = None
+    l2_note = f"inputs {in_bytes / 2**20:.0f} MiB per GPU > 126 MB L2 (no flush needed)"
+    if in_bytes < 2 * 126e6:
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)
+        l2_note = (f"inputs {in_bytes / 2**20:.0f} MiB per GPU fit in the 126 MB L2: a 256 MiB buffer is overwritten before "
+                   "every timed step, outside the per-step CUDA events that are summed")
 
     def step():
         out = flash_attn_unpadded_qkvpacked_func(qkv, cu, s, p, causal=causal)
@@ -257,6 +264,8 @@ def run_ours(args, w):
     t_end = torch.cuda.Event(enable_timing=True)
     t_start.record()
     for i in range(args.steps):
+        if flush is not None:
+            flush.zero_()
         ev[i][0].record()
         out = flash_attn_unpadded_qkvpacked_func(qkv, cu, s, p, causal=causal)
         ev[i][1].record()
@@ -269,6 +278,8 @@ def run_ours(args, w):
     kt = flash_attn_cuda.kernel_timing_collect()
     clocks = sampler.stop() if sampler else None
     ms_total = t_start.elapsed_time(t_end)
+    if flush is not None:
+        ms_total = sum(e[0].elapsed_time(e[2]) for e in ev)
     fwd_ms = sum(e[0].elapsed_time(e[1]) for e in ev) / args.steps
     bwd_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / args.steps
 
@@ -358,7 +369,7 @@ def run_ours(args, w):
             "scaling": "weak", "vs_baseline": None, "dtype": w["dtype"], "data": "synthetic",
             "config": {"workload": w["name"], "global_batch": w["b"] * world, "seq_len": s,
                        "parallelism": f"(batch x heads) units sharded over {world} GPU(s), no collective",
-                       "l2": f"inputs {in_bytes / 2**20:.0f} MiB per GPU > 126 MB L2 (no flush needed)",
+                       "l2": l2_note,
                        "per_gpu_tflops": value / world, "fwd_ms": fwd_ms, "bwd_ms": bwd_ms,
                        "fwd_tflops": f_fwd / (fwd_ms * 1e-3) / 1e12, "bwd_tflops": 2.5 * f_fwd / (bwd_ms * 1e-3) / 1e12,
                        "fwd_kernel_ms": kf_ms, "bwd_kernel_ms": kb_ms,
