@@ -59,8 +59,15 @@ __device__ long long g_fwd_trace[64 * 32];
   do {                                                                                                     \
     if (trace_cta && (u_) < 64 && (threadIdx.x & 31) == 0) g_fwd_trace[(u_) * 32 + (slot)] = clock64();   \
   } while (0)
+__device__ long long g_fwd_cta[8192 * 8];   // per CTA: smid, globaltimer start, clock start, after setup, loop end (tile 1), end, globaltimer end, K blocks
+#define FA_FCTA(slot, val)                                                                    \
+  do {                                                                                        \
+    const int cta_lin = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);       \
+    if (cta_lin < 8192) g_fwd_cta[cta_lin * 8 + (slot)] = (val);                              \
+  } while (0)
 #else
 #define FA_FTRACE(u_, slot) do { } while (0)
+#define FA_FCTA(slot, val) do { } while (0)
 #endif
 
 template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse>
@@ -88,6 +95,13 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
   if (q0 >= seq.seqlen_q) return;   // CTA-uniform
 #ifdef FA_BWD_TRACE
   const bool trace_cta = bidb == 0 && bidh == 0 && m_block == n_mblocks - 1;
+  if (threadIdx.x == 0) {
+    uint32_t smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    FA_FCTA(0, (long long)smid);
+    FA_FCTA(1, (long long)global_timer_ns());
+    FA_FCTA(2, clock64());
+  }
 #endif
 
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
@@ -170,6 +184,7 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  if (threadIdx.x == 0) FA_FCTA(3, clock64());
 
   uint8_t* sQ = smem + L::kQOff;
   uint8_t* sK = smem + L::kKOff;
@@ -422,6 +437,7 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
       if ((warp & 3) == 0) FA_FTRACE(u, 8 * t + 5);
     }
 
+    if (threadIdx.x == 128) { FA_FCTA(4, clock64()); FA_FCTA(7, (long long)nu); }
     // ---- epilogue: O = acc / l (x 1/keep), lse = m*scale + ln(l) ----
     if (my_cnt > 0 || (q0 + t * kBlockM) < seq.seqlen_q) {
       const bool dead = (l == 0.f) || (l != l);
@@ -449,6 +465,12 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
   }
+#ifdef FA_BWD_TRACE
+  if (threadIdx.x == 0) {
+    FA_FCTA(5, clock64());
+    FA_FCTA(6, (long long)global_timer_ns());
+  }
+#endif
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -471,6 +493,9 @@ PFN_cuTensorMapEncodeTiled_v12000 get_tensor_map_encoder() {
 #ifdef FA_BWD_TRACE
 extern "C" __attribute__((visibility("default"))) int fa_debug_read_fwd_trace(long long* host, int n) {
   return (int)cudaMemcpyFromSymbol(host, g_fwd_trace, sizeof(long long) * n);
+}
+extern "C" __attribute__((visibility("default"))) int fa_debug_read_fwd_cta(long long* host, int n) {
+  return (int)cudaMemcpyFromSymbol(host, g_fwd_cta, sizeof(long long) * n);
 }
 #endif
 

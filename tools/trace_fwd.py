@@ -39,3 +39,33 @@ for nm, a, bb in (("ld", 0, 1), ("max+rescale", 1, 2), ("turn wait", 2, 3), ("ex
         print(f"A {nm}: median {sorted(vals)[len(vals) // 2]}")
 vals = [T[u + 1][0] - T[u][5] for u in range(4, 28) if T[u + 1][0] > 0 and T[u][5] > 0]
 print("A P handed -> next s_full: median", sorted(vals)[len(vals) // 2])
+
+# ---- per-CTA lifetimes ----
+import statistics
+ncta = min(8192, ((s + 255) // 256) * h * b)
+cb = (ctypes.c_longlong * (ncta * 8))()
+flash_attn_cuda._lib.fa_debug_read_fwd_cta.argtypes = [ctypes.c_void_p, ctypes.c_int]
+assert flash_attn_cuda._lib.fa_debug_read_fwd_cta(cb, ncta * 8) == 0
+C = [[cb[i * 8 + j] for j in range(8)] for i in range(ncta)]
+C = [c for c in C if c[5] > 0 and c[4] > 0 and c[7] > 0]
+print("CTAs", len(C))
+print("median clk: setup %d  loop %d (%.0f per K block, median %d blocks)  epilogue %d  total %d" % (
+    statistics.median(c[3] - c[2] for c in C), statistics.median(c[4] - c[3] for c in C),
+    statistics.median((c[4] - c[3]) / c[7] for c in C), statistics.median(c[7] for c in C),
+    statistics.median(c[5] - c[4] for c in C), statistics.median(c[5] - c[2] for c in C)))
+# fixed cost per CTA from a linear fit of loop time against the number of K blocks
+xs, ys = [c[7] for c in C], [c[5] - c[2] for c in C]
+if len(set(xs)) > 1:
+    mx, my = sum(xs) / len(xs), sum(ys) / len(ys)
+    slope = sum((x - mx) * (y - my) for x, y in zip(xs, ys)) / sum((x - mx) ** 2 for x in xs)
+    print("linear fit: CTA clk = %.0f + %.0f * K blocks" % (my - slope * mx, slope))
+by_sm = {}
+for c in C:
+    by_sm.setdefault(c[0], []).append(c)
+gaps = []
+for sm, l in by_sm.items():
+    l.sort(key=lambda c: c[1])
+    for a, bb in zip(l, l[1:]):
+        gaps.append(bb[1] - a[6])
+if gaps:
+    print("per-SM: CTAs/SM %.1f  median gap between CTAs %.2f us  max %.2f us" % (len(C) / len(by_sm), statistics.median(gaps) / 1e3, max(gaps) / 1e3))
