@@ -193,7 +193,14 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
   }
   auto tile_of = [&](int it) -> int { return kSparse ? static_cast<int>(tile_list[it]) : m_start + it; };
 
-  if (threadIdx.x == 0) {
+  uint8_t* sK = smem + L::kKOff;
+  uint8_t* sV = smem + L::kVOff;
+  uint8_t* sQ = smem + L::kQOff;
+  uint8_t* sDo = smem + L::kDoOff;
+  float* sStat = reinterpret_cast<float*>(smem + L::kStatOff);
+  if (warp == 13 && elect_one()) {
+    // The TMA loader initialises the barriers of its own loads and starts K, V and the first Q / dO tile right away:
+    // the loads run under the TMEM allocation and the CTA-wide barrier below instead of after them.
     mbar_init(k_full, 1);
     mbar_init(v_full, 1);
     for (int s = 0; s < kQ; ++s) {
@@ -202,6 +209,34 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     }
     mbar_init(do_full, 1);
     mbar_init(do_empty, 1);
+    fence_mbar_init();
+    tma_prefetch_desc(&maps.q);
+    tma_prefetch_desc(&maps.k);
+    tma_prefetch_desc(&maps.v);
+    tma_prefetch_desc(&maps.dout);
+    if (n_iter > 0) {   // nobody waits for K / V otherwise, and a CTA must not exit with loads in flight
+      mbar_arrive_expect_tx(k_full, L::kTile);
+#pragma unroll
+      for (int c = 0; c < DPAD / 64; ++c) tma_load_3d(sK + c * L::kSub, &maps.k, k_full, c * 64, bidh, seq.k_begin + k0);
+      const int m = tile_of(0);
+      mbar_arrive_expect_tx(&q_full[0], L::kTile + 1024);
+#pragma unroll
+      for (int c = 0; c < DPAD / 64; ++c)
+        tma_load_3d(sQ + c * L::kSub, &maps.q, &q_full[0], c * 64, bidh, seq.q_begin + m * kBM);
+      const int64_t stat_off = (int64_t)bh * ws.sq_pad + m * kBM;
+      bulk_load_1d(sStat, ws.nl + stat_off, 512, &q_full[0]);
+      bulk_load_1d(sStat + 128, ws.dsum + stat_off, 512, &q_full[0]);
+      mbar_arrive_expect_tx(v_full, L::kTile);
+#pragma unroll
+      for (int c = 0; c < DPAD / 64; ++c) tma_load_3d(sV + c * L::kSub, &maps.v, v_full, c * 64, bidh, seq.k_begin + k0);
+      mbar_arrive_expect_tx(do_full, L::kTile);
+#pragma unroll
+      for (int c = 0; c < DPAD / 64; ++c)
+        tma_load_3d(sDo + c * L::kSub, &maps.dout, do_full, c * 64, bidh, seq.q_begin + m * kBM);
+    }
+  }
+  __syncwarp();
+  if (threadIdx.x == 0) {
     mbar_init(s_full, 1);
     mbar_init(dp_full, 1);
     mbar_init(p_full, 256);
@@ -222,13 +257,8 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
   const uint32_t tmem_base = *tmem_ptr_smem;
   if (threadIdx.x == 0) FA_CTA_MARK(3, clock64());
 
-  uint8_t* sK = smem + L::kKOff;
-  uint8_t* sV = smem + L::kVOff;
-  uint8_t* sQ = smem + L::kQOff;
-  uint8_t* sDo = smem + L::kDoOff;
   uint8_t* sDs = smem + L::kDsOff;
   uint8_t* sDq = smem + L::kDqOff;
-  float* sStat = reinterpret_cast<float*>(smem + L::kStatOff);
   uint32_t* sMask = reinterpret_cast<uint32_t*>(smem + L::kMaskOff);
 
   constexpr uint32_t kColS = 0, kColDP = 128, kColDV = 256, kColDK = 384;
@@ -242,19 +272,8 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     if (warp == 13) {
       // ===================================== TMA loader ========================================
       if (elect_one()) {
-        tma_prefetch_desc(&maps.q);
-        tma_prefetch_desc(&maps.k);
-        tma_prefetch_desc(&maps.v);
-        tma_prefetch_desc(&maps.dout);
-        if (n_iter > 0) {   // nobody waits for K / V otherwise, and a CTA must not exit with loads in flight
-          mbar_arrive_expect_tx(k_full, L::kTile);
-#pragma unroll
-          for (int c = 0; c < DPAD / 64; ++c) tma_load_3d(sK + c * L::kSub, &maps.k, k_full, c * 64, bidh, seq.k_begin + k0);
-          mbar_arrive_expect_tx(v_full, L::kTile);
-#pragma unroll
-          for (int c = 0; c < DPAD / 64; ++c) tma_load_3d(sV + c * L::kSub, &maps.v, v_full, c * 64, bidh, seq.k_begin + k0);
-        }
-        for (int it = 0; it < n_iter; ++it) {
+        // K, V and tile 0 were issued before the CTA-wide barrier
+        for (int it = 1; it < n_iter; ++it) {
           const int m = tile_of(it);
           const int s = it % kQ;
           mbar_wait(&q_empty[s], ((it / kQ) & 1) ^ 1);

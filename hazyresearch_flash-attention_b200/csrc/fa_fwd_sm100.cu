@@ -160,14 +160,23 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
     for (int t = 0; t < kTilesPerCta; ++t) cnt[t] = cnt[t] > 0 ? nu : 0;
   }
 
+  uint8_t* sQ = smem + L::kQOff;
+  uint8_t* sK = smem + L::kKOff;
+  uint8_t* sV = smem + L::kVOff;
   if (threadIdx.x == 0) {
 #pragma unroll
     for (int t = 0; t < 2; ++t) {
-      mbar_init(&q_full[t], 1);
       mbar_init(&s_full[t], 1);
       for (int c = 0; c < kPChunks; ++c) mbar_init(&p_full[t * kPChunks + c], kBlockM);
       mbar_init(&o_full[t], 1);
     }
+    fence_mbar_init();
+  }
+  if (warp == 8 && elect_one()) {
+    // The TMA producer initialises the barriers of its own loads and starts Q and the first K / V block right away:
+    // the loads run under the TMEM allocation and the CTA-wide barrier below instead of after them.
+    mbar_init(&q_full[0], 1);
+    mbar_init(&q_full[1], 1);
     for (int s = 0; s < ST; ++s) {
       mbar_init(&k_full[s], 1);
       mbar_init(&k_empty[s], 1);
@@ -175,7 +184,32 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
       mbar_init(&v_empty[s], 1);
     }
     fence_mbar_init();
+    tma_prefetch_desc(&maps.q);
+    tma_prefetch_desc(&maps.k);
+    tma_prefetch_desc(&maps.v);
+#pragma unroll
+    for (int t = 0; t < kTilesPerCta; ++t) {
+      if (cnt[t] > 0) {
+        mbar_arrive_expect_tx(&q_full[t], L::kTileBytes);
+#pragma unroll
+        for (int c = 0; c < DPAD / 64; ++c)
+          tma_load_3d(sQ + t * L::kTileBytes + c * L::kSubTileBytes, &maps.q, &q_full[t], c * 64, bidh,
+                      seq.q_begin + q0 + t * kBlockM);
+      }
+    }
+    if (nu > 0) {
+      const int j0 = kSparse ? blk_list[0] : 0;
+      mbar_arrive_expect_tx(&k_full[0], L::kTileBytes);
+#pragma unroll
+      for (int c = 0; c < DPAD / 64; ++c)
+        tma_load_3d(sK + c * L::kSubTileBytes, &maps.k, &k_full[0], c * 64, bidh, seq.k_begin + j0 * kBlockN);
+      mbar_arrive_expect_tx(&v_full[0], L::kTileBytes);
+#pragma unroll
+      for (int c = 0; c < DPAD / 64; ++c)
+        tma_load_3d(sV + c * L::kSubTileBytes, &maps.v, &v_full[0], c * 64, bidh, seq.k_begin + j0 * kBlockN);
+    }
   }
+  __syncwarp();
   if (warp == 0) {
     tmem_alloc(tmem_ptr_smem, 512);
     tmem_relinquish();
@@ -186,29 +220,13 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
   const uint32_t tmem_base = *tmem_ptr_smem;
   if (threadIdx.x == 0) FA_FCTA(3, clock64());
 
-  uint8_t* sQ = smem + L::kQOff;
-  uint8_t* sK = smem + L::kKOff;
-  uint8_t* sV = smem + L::kVOff;
 
   if (warp >= 8) {
     setmaxnreg_dec<kOtherRegs>();
     if (warp == 8) {
       // ===================================== TMA producer =====================================
       if (elect_one()) {
-        tma_prefetch_desc(&maps.q);
-        tma_prefetch_desc(&maps.k);
-        tma_prefetch_desc(&maps.v);
-#pragma unroll
-        for (int t = 0; t < kTilesPerCta; ++t) {
-          if (cnt[t] > 0) {
-            mbar_arrive_expect_tx(&q_full[t], L::kTileBytes);
-#pragma unroll
-            for (int c = 0; c < DPAD / 64; ++c)
-              tma_load_3d(sQ + t * L::kTileBytes + c * L::kSubTileBytes, &maps.q, &q_full[t], c * 64, bidh,
-                          seq.q_begin + q0 + t * kBlockM);
-          }
-        }
-        for (int u = 0; u < nu; ++u) {
+        for (int u = 1; u < nu; ++u) {   // Q and block 0 were issued before the CTA-wide barrier
           const int j = kSparse ? blk_list[u] : u;
           const int s = u % ST;
           const uint32_t ph = (u / ST) & 1;
