@@ -126,7 +126,22 @@ def seqlen_k_rounded(max_seqlen_k, head_size):
 
 
 def _check_qkv(q, k, v, cu_seqlens_q, cu_seqlens_k):
-    # the TORCH_CHECKs of fmha_api.cpp:135-170
+    """The TORCH_CHECKs of fmha_api.cpp:135-170.  One combined test on the hot path (a Python call per check costs
+    ~1 us, 17 of them per forward and again per backward); the itemised checks only run to produce the message."""
+    qs, ks, dt = q.shape, k.shape, q.dtype
+    if (q.is_cuda and k.is_cuda and v.is_cuda and cu_seqlens_q.is_cuda and cu_seqlens_k.is_cuda
+            and (dt is torch.float16 or dt is torch.bfloat16) and k.dtype is dt and v.dtype is dt
+            and cu_seqlens_q.dtype is torch.int32 and cu_seqlens_k.dtype is torch.int32
+            and len(qs) == 3 and len(ks) == 3 and v.shape == ks and ks[1:] == qs[1:]
+            and q.stride(2) == 1 and k.stride(2) == 1 and v.stride(2) == 1
+            and cu_seqlens_q.is_contiguous() and cu_seqlens_k.is_contiguous()
+            and qs[2] % 8 == 0 and qs[2] <= 128
+            and cu_seqlens_q.numel() > 1 and cu_seqlens_k.numel() == cu_seqlens_q.numel()):
+        return cu_seqlens_q.numel() - 1, qs[0], ks[0], qs[1], qs[2]
+    return _check_qkv_itemised(q, k, v, cu_seqlens_q, cu_seqlens_k)
+
+
+def _check_qkv_itemised(q, k, v, cu_seqlens_q, cu_seqlens_k):
     _check(q.is_cuda and k.is_cuda and v.is_cuda, "q, k, v must be CUDA tensors")
     _check(q.dtype in (torch.float16, torch.bfloat16), "q must be fp16 or bf16")
     _check(k.dtype == q.dtype and v.dtype == q.dtype, "q, k, v must have the same dtype")
@@ -166,11 +181,11 @@ def _philox_state(p_dropout, gen, device, params):
 
 def _fill_common(P, q, k, v, cu_seqlens_q, cu_seqlens_k, b, h, d, total_q, total_k, max_seqlen_q, max_seqlen_k,
                  p_dropout, softmax_scale, is_causal):
-    P.q, P.k, P.v = _ptr(q), _ptr(k), _ptr(v)
-    P.q_row_stride, P.q_head_stride = q.stride(0), q.stride(1)
-    P.k_row_stride, P.k_head_stride = k.stride(0), k.stride(1)
-    P.v_row_stride, P.v_head_stride = v.stride(0), v.stride(1)
-    P.cu_seqlens_q, P.cu_seqlens_k = _ptr(cu_seqlens_q), _ptr(cu_seqlens_k)
+    P.q, P.k, P.v = q.data_ptr(), k.data_ptr(), v.data_ptr()
+    P.q_row_stride, P.q_head_stride, _ = q.stride()
+    P.k_row_stride, P.k_head_stride, _ = k.stride()
+    P.v_row_stride, P.v_head_stride, _ = v.stride()
+    P.cu_seqlens_q, P.cu_seqlens_k = cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr()
     P.b, P.h, P.d, P.total_q, P.total_k = b, h, d, total_q, total_k
     P.max_seqlen_q, P.max_seqlen_k = max_seqlen_q, max_seqlen_k
     P.seqlen_q_rounded = _round_multiple(max_seqlen_q, 16)
@@ -256,13 +271,21 @@ def _fwd_impl(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, p
 def _bwd_impl(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seqlens_k, max_seqlen_q,
               max_seqlen_k, p_dropout, softmax_scale, zero_tensors, is_causal, gen, blockmask=None):
     b, total_q, total_k, h, d = _check_qkv(q, k, v, cu_seqlens_q, cu_seqlens_k)
-    _check(dout.is_cuda and out.is_cuda and dq.is_cuda and dk.is_cuda and dv.is_cuda, "all tensors must be CUDA")
-    for name, t, shape in (("dout", dout, (total_q, h, d)), ("out", out, (total_q, h, d)),
-                           ("dq", dq, (total_q, h, d)), ("dk", dk, (total_k, h, d)), ("dv", dv, (total_k, h, d))):
-        _check(t.dtype == q.dtype, f"{name} must have the dtype of q")
-        _check(tuple(t.shape) == shape, f"{name} has the wrong shape")
-    _check(softmax_lse.dtype == torch.float32 and softmax_lse.is_contiguous(), "softmax_lse must be contiguous fp32")
-    _check(dq.stride(-1) == 1 and dk.stride(-1) == 1 and dv.stride(-1) == 1, "last dim of dq, dk, dv must be contiguous")
+    dt, q_shape, k_shape = q.dtype, (total_q, h, d), (total_k, h, d)
+    if not (dout.is_cuda and out.is_cuda and dq.is_cuda and dk.is_cuda and dv.is_cuda
+            and dout.dtype is dt and out.dtype is dt and dq.dtype is dt and dk.dtype is dt and dv.dtype is dt
+            and dout.shape == q_shape and out.shape == q_shape and dq.shape == q_shape
+            and dk.shape == k_shape and dv.shape == k_shape
+            and softmax_lse.dtype is torch.float32 and softmax_lse.is_contiguous()
+            and dq.stride(2) == 1 and dk.stride(2) == 1 and dv.stride(2) == 1):
+        # itemised only to produce the message (see _check_qkv)
+        _check(dout.is_cuda and out.is_cuda and dq.is_cuda and dk.is_cuda and dv.is_cuda, "all tensors must be CUDA")
+        for name, t, shape in (("dout", dout, q_shape), ("out", out, q_shape), ("dq", dq, q_shape), ("dk", dk, k_shape),
+                               ("dv", dv, k_shape)):
+            _check(t.dtype == q.dtype, f"{name} must have the dtype of q")
+            _check(tuple(t.shape) == shape, f"{name} has the wrong shape")
+        _check(softmax_lse.dtype == torch.float32 and softmax_lse.is_contiguous(), "softmax_lse must be contiguous fp32")
+        _check(dq.stride(-1) == 1 and dk.stride(-1) == 1 and dv.stride(-1) == 1, "last dim of dq, dk, dv must be contiguous")
     if dout.stride(-1) != 1:
         dout = dout.contiguous()
     if out.stride(-1) != 1:
@@ -275,11 +298,11 @@ def _bwd_impl(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seql
         softmax_d = torch.empty((b, h, P.seqlen_q_rounded), dtype=torch.float32, device=q.device)
         if zero_tensors:
             dq.zero_(), dk.zero_(), dv.zero_(), softmax_d.zero_()
-        P.o, P.o_row_stride, P.o_head_stride = out.data_ptr(), out.stride(0), out.stride(1)
-        P.dout, P.do_row_stride, P.do_head_stride = dout.data_ptr(), dout.stride(0), dout.stride(1)
-        P.dq, P.dq_row_stride, P.dq_head_stride = dq.data_ptr(), dq.stride(0), dq.stride(1)
-        P.dk, P.dk_row_stride, P.dk_head_stride = dk.data_ptr(), dk.stride(0), dk.stride(1)
-        P.dv, P.dv_row_stride, P.dv_head_stride = dv.data_ptr(), dv.stride(0), dv.stride(1)
+        P.o, (P.o_row_stride, P.o_head_stride, _) = out.data_ptr(), out.stride()
+        P.dout, (P.do_row_stride, P.do_head_stride, _) = dout.data_ptr(), dout.stride()
+        P.dq, (P.dq_row_stride, P.dq_head_stride, _) = dq.data_ptr(), dq.stride()
+        P.dk, (P.dk_row_stride, P.dk_head_stride, _) = dk.data_ptr(), dk.stride()
+        P.dv, (P.dv_row_stride, P.dv_head_stride, _) = dv.data_ptr(), dv.stride()
         P.softmax_lse, P.softmax_d = softmax_lse.data_ptr(), softmax_d.data_ptr()
         op = FA_OP_BWD
         if blockmask is not None:
