@@ -415,14 +415,14 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
       for (int ch = 0; ch < kPChunks; ++ch) {
 #pragma unroll
         for (int c = ch * kCw; c < (ch + 1) * kCw; c += 4) {
-          sv[c] = ex2(fmaf(sv[c], scale_log2, neg_ms));
-          sv[c + 1] = ex2(fmaf(sv[c + 1], scale_log2, neg_ms));
-          sv[c + 2] = ex2(fmaf(sv[c + 2], scale_log2, neg_ms));
-          sv[c + 3] = ex2(fmaf(sv[c + 3], scale_log2, neg_ms));
-          sum0 += sv[c];
-          sum1 += sv[c + 1];
-          sum2 += sv[c + 2];
-          sum3 += sv[c + 3];
+          ffma2(sv[c], sv[c + 1], scale_log2, neg_ms);          // packed pairs: half the issue slots of FFMA / FADD
+          ffma2(sv[c + 2], sv[c + 3], scale_log2, neg_ms);
+          sv[c] = ex2(sv[c]);
+          sv[c + 1] = ex2(sv[c + 1]);
+          sv[c + 2] = ex2(sv[c + 2]);
+          sv[c + 3] = ex2(sv[c + 3]);
+          fadd2(sum0, sum1, sv[c], sv[c + 1]);
+          fadd2(sum2, sum3, sv[c + 2], sv[c + 3]);
         }
         if (kDropout) {
 #pragma unroll

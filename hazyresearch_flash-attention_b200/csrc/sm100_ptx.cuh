@@ -281,6 +281,22 @@ FA_DEVICE float ex2(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// Packed fp32 pairs (FFMA2 / FADD2 on sm_100): two results per issue slot.  Same rounding as the scalar forms.
+FA_DEVICE void ffma2(float& a0, float& a1, float s, float b) {   // (a0, a1) = (a0, a1) * s + b
+  uint64_t in, sc, bb, out;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(in) : "f"(a0), "f"(a1));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(sc) : "f"(s), "f"(s));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(bb) : "f"(b), "f"(b));
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(out) : "l"(in), "l"(sc), "l"(bb));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a0), "=f"(a1) : "l"(out));
+}
+FA_DEVICE void fadd2(float& a0, float& a1, float b0, float b1) {   // (a0, a1) += (b0, b1)
+  uint64_t x, y, out;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(x) : "f"(a0), "f"(a1));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(y) : "f"(b0), "f"(b1));
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(out) : "l"(x), "l"(y));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a0), "=f"(a1) : "l"(out));
+}
 template <bool kBf16>
 FA_DEVICE uint32_t pack2(float lo, float hi) {   // round-to-nearest-even pack of two floats into 16-bit pair
   uint32_t r;
