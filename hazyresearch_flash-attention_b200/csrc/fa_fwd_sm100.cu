@@ -554,11 +554,11 @@ cudaError_t launch_fwd_variant(const FwdTensorMaps& maps, const fa_params& p, co
   const int n_mblocks = (p.max_seqlen_q + kBlockM * kTilesPerCta - 1) / (kBlockM * kTilesPerCta);
   const dim3 grid = kCausal ? dim3(n_mblocks * p.h * p.b, 1, 1) : dim3(n_mblocks, p.h, p.b);
   const int bh_group = causal_bh_group(p.max_seqlen_q > p.max_seqlen_k ? p.max_seqlen_q : p.max_seqlen_k);
-  // exponential-phase ping-pong (see the kernel).  Measured (profiles/r01_kernel_experiments_ab.log): +10 % at d = 64,
-  // +1.5 % at d = 128 causal, -3 % at d = 128 non-causal (there the second tile fills the MUFU bubbles the first one
-  // leaves around its TMEM stores better than the turn token does), neutral with dropout (issue-bound, not MUFU-bound).
+  // exponential-phase ping-pong (see the kernel).  Measured (profiles/r01_kernel_experiments_ab.log, after the FFMA2 change):
+  // +7-10 % at d = 64 (+1-7 % with dropout); at d = 128 neutral (causal) to -3 % (non-causal): there the second tile fills
+  // the MUFU bubbles the first one leaves around its TMEM stores better than the turn token does.  So: d <= 64 only.
   const char* pp_env = getenv("FA_FWD_PINGPONG");
-  const int pingpong = pp_env != nullptr ? atoi(pp_env) : ((!kDropout && (DPAD == 64 || kCausal)) ? 1 : 0);
+  const int pingpong = pp_env != nullptr ? atoi(pp_env) : (DPAD == 64 ? 1 : 0);
   void* span = timing_begin(stream);
   kernel<<<grid, kNumThreads, smem, stream>>>(maps, p, bm, n_mblocks, bh_group, pingpong, make_philox_key(p.philox_seed, p.philox_offset));
   timing_end(span, 0, stream);
