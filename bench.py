@@ -130,8 +130,12 @@ def run_reference(args, w):
         step()
     dt = (time.perf_counter() - t0) / args.steps
     val = flops / dt / 1e12
-    sample = f"b={sample_b} h={sample_h} slice of the workload's (b{w['b']}, h{w['h']}) units, fp32, per step"
-    line = {"impl": "reference", "metric": "attn fwd+bwd TFLOP/s per GPU", "value": val, "unit": "TFLOP/s",
+    sample = (f"b={sample_b} h={sample_h} slice (the first sequence, the first two heads; 1/{w['b'] * w['h'] // (sample_b * sample_h)} of the "
+              f"workload's (b{w['b']}, h{w['h']}) independent units -- the fp32 scores of one unit are 64 MiB, the full set would "
+              f"not fit a step of seconds) per step, fp32; value = FLOPs of the slice / its time, so the ratio to the GPU arm "
+              f"is a throughput ratio (FLOP-normalised), not a same-work time ratio")
+    line = {"impl": "reference", "metric": "attn fwd+bwd TFLOP/s, whole job (sum over the GPUs; per GPU: config.per_gpu_tflops)",
+            "value": val, "unit": "TFLOP/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
             "config": {"workload": w["name"], "sample": sample},
@@ -141,26 +145,53 @@ def run_reference(args, w):
     print(json.dumps(line), flush=True)
 
 
-def run_ring(args, w):
-    """One long causal sequence sharded over the ranks (strong scaling): flash_attn/ring_attention.py."""
-    import flash_attn_cuda
-    import torch.distributed as dist
+def ring_parity_check(world, rank, device, dist):
+    """Before any ring number is reported: one small causal problem through the ring on all ranks, gathered and compared
+    on rank 0 with the single-GPU kernels on the unsharded sequence (O, dQ, dK, dV).  Raises on mismatch."""
     from flash_attn import ring_attention as ring
+    from flash_attn.flash_attn_interface import flash_attn_unpadded_func
+    b, h, d, c = 1, 12, 128, 512
+    S = 2 * world * c
+    g = torch.Generator(device=device).manual_seed(4242)      # same seed on every rank: everyone holds the full problem
+    q, k, v, dout = [torch.randn(b, S, h, d, device=device, dtype=torch.bfloat16, generator=g) for _ in range(4)]
+    ql, kl, vl = [ring.zigzag_shard(t, world, rank).requires_grad_() for t in (q, k, v)]
+    out = ring.ring_flash_attn_func(ql, kl, vl)
+    grads = torch.autograd.grad(out, (ql, kl, vl), ring.zigzag_shard(dout, world, rank))
+    full = []
+    for t in (out.detach(),) + tuple(grads):
+        parts = [torch.empty_like(t) for _ in range(world)]
+        if world > 1:
+            dist.all_gather(parts, t.contiguous())
+        else:
+            parts = [t]
+        full.append(ring.zigzag_unshard(parts))
+    errs = None
+    if rank == 0:
+        q1, k1, v1 = [t.reshape(b * S, h, d).clone().requires_grad_() for t in (q, k, v)]
+        cu = torch.arange(0, (b + 1) * S, S, device=device, dtype=torch.int32)
+        o1 = flash_attn_unpadded_func(q1, k1, v1, cu, cu, S, S, 0.0, causal=True)
+        g1 = torch.autograd.grad(o1, (q1, k1, v1), dout.reshape(b * S, h, d))
+        errs = {}
+        for name, got, ref in zip(("O", "dQ", "dK", "dV"), full, (o1.detach(),) + tuple(g1)):
+            ref = ref.reshape(b, S, h, d).float()
+            err = (got.float() - ref).abs().max().item()
+            tol = 2e-2 * max(1.0, ref.abs().max().item())      # a few 16-bit ulps of the largest entry
+            errs[name] = err
+            if not err <= tol:
+                raise AssertionError(f"ring parity check failed at world {world}: {name} max error {err:.3e} > {tol:.3e}")
+    return errs
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local_rank)
-    device = torch.device("cuda", local_rank)
-    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-    os.environ.setdefault("MASTER_PORT", "29533")
-    dist.init_process_group("nccl" if world > 1 else "gloo", rank=rank, world_size=world,
-                            **({"device_id": device} if world > 1 else {}))
+
+def ring_record(args, w, world, rank, local_rank, device, dist, steps, warmup):
+    """ONE 64K-token causal problem sequence-sharded (zig-zag) over the ranks: strong scaling.  -> dict (rank 0) or None."""
+    import flash_attn_cuda
+    from flash_attn import ring_attention as ring
+    errs = ring_parity_check(world, rank, device, dist)
     b, h, d, s = w["b"], w["h"], w["d"], w["s"]
     c = s // (2 * world)
     g = torch.Generator(device=device).manual_seed(99 + rank)
-    q, k, v = [torch.randn(2, b, c, h, d, device=device, dtype=torch.bfloat16, generator=g).requires_grad_() for _ in range(3)]
-    dout = torch.randn(2, b, c, h, d, device=device, dtype=torch.bfloat16, generator=g)
+    q, k, v = [torch.randn(b, 2, c, h, d, device=device, dtype=torch.bfloat16, generator=g).requires_grad_() for _ in range(3)]
+    dout = torch.randn(b, 2, c, h, d, device=device, dtype=torch.bfloat16, generator=g)
 
     def step():
         out = ring.ring_flash_attn_func(q, k, v)
@@ -171,42 +202,120 @@ def run_ring(args, w):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         step()
     barrier()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
-    if sampler:
-        sampler.start()
     launches0 = flash_attn_cuda._lib.fa_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(args.steps):
+    for _ in range(steps):
         step()
     e1.record()
     barrier()
     launches = flash_attn_cuda._lib.fa_launch_count() - launches0
-    clocks = sampler.stop() if sampler else None
     t = torch.tensor([e0.elapsed_time(e1)], device=device, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_step = t.item() / args.steps
-    f_step = 3.5 * flops_fwd(b, h, s, s, d, True)
+    if rank != 0:
+        return None
+    ms_step = t.item() / steps
+    value = 3.5 * flops_fwd(b, h, s, s, d, True) / (ms_step * 1e-3) / 1e12
+    peaks = load_peaks()
+    return {"metric": "attn fwd+bwd TFLOP/s, whole job (ONE sequence sharded over the GPUs)", "value": value, "unit": "TFLOP/s",
+            "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": ms_step, "scaling": "strong",
+            "workload": w["name"], "per_gpu_tflops": value / world,
+            "frac_of_bf16_peak_per_gpu": value / world / peaks["burst"],
+            "kv_block_bytes_per_hop": 2 * 2 * b * c * h * d * 2, "dkv_block_bytes_per_hop": 2 * 2 * b * c * h * d * 4,
+            "exchange": "K/V (bf16) and, in the backward, the fp32 dK/dV accumulator rotate rank->rank+1 with NCCL P2P; each "
+                        "transfer overlaps an attention kernel (K/V: the same step's, dK/dV: the next step's)",
+            "parity_check_max_abs_err": errs, "gpu_launches_per_step": launches / steps,
+            "l2": "per-GPU inputs exceed L2 at every N <= 8 (no flush needed)"}
+
+
+def run_ring(args, w):
+    """--workload ring64k: the ring record as the bench line itself."""
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29533")
+    dist.init_process_group("nccl" if world > 1 else "gloo", rank=rank, world_size=world,
+                            **({"device_id": device} if world > 1 else {}))
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    rec = ring_record(args, w, world, rank, local_rank, device, dist, args.steps, args.warmup)
+    clocks = sampler.stop() if sampler else None
     if rank == 0:
-        peaks = load_peaks()
-        value = f_step / (ms_step * 1e-3) / 1e12
-        kv_bytes = 2 * 2 * b * c * h * d * 2
-        print(json.dumps({
-            "metric": "attn fwd+bwd TFLOP/s (aggregate)", "value": value, "unit": "TFLOP/s", "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": w["name"], "global_batch": b, "seq_len": s,
-                       "parallelism": f"sequence sharded zig-zag over {world} GPU(s); K/V (+ fp32 dK/dV in the backward) "
-                                      f"blocks rotate rank->rank+1 with NCCL P2P on a side stream",
-                       "kv_block_bytes_per_hop": kv_bytes, "per_gpu_tflops": value / world,
-                       "frac_of_bf16_peak_per_gpu": value / world / peaks["burst"],
-                       "l2": "per-GPU inputs exceed L2 at every N <= 8 (no flush needed)"},
-            "gpu_launches": int(launches), "clocks": clocks}), flush=True)
+        rec.update({"higher_is_better": True, "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+                    "config": {"workload": w["name"], "global_batch": w["b"], "seq_len": w["s"],
+                               "parallelism": f"sequence sharded zig-zag over {world} GPU(s)"},
+                    "gpu_launches": int(rec["gpu_launches_per_step"] * args.steps), "clocks": clocks})
+        print(json.dumps(rec), flush=True)
     dist.destroy_process_group()
+
+
+def sub_record(wname, device, steps=10, warmup=3):
+    """A further BASELINE.json configuration timed like the headline (inputs resident, CUDA events on the launching
+    stream, L2 flushed between steps when the inputs fit in it), reported as a sub-record of the bench line."""
+    import flash_attn_cuda
+    from flash_attn.flash_attn_interface import flash_attn_unpadded_qkvpacked_func
+    w = WORKLOADS[wname]
+    qkv, dout, cu = make_batch(w, device, seed=77)
+    qkv.requires_grad_()
+    s, p, causal = w["s"], w["p"], w["causal"]
+    f_fwd = flops_fwd(w["b"], w["h"], s, s, w["d"], causal)
+    in_bytes = qkv.numel() * qkv.element_size() + dout.numel() * dout.element_size()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=device) if in_bytes < 2 * 126e6 else None
+
+    def step():
+        out = flash_attn_unpadded_qkvpacked_func(qkv, cu, s, p, causal=causal)
+        torch.autograd.grad(out, qkv, dout)
+
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    flash_attn_cuda.kernel_timing(True)
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(steps)]
+    for i in range(steps):
+        if flush is not None:
+            flush.zero_()
+        ev[i][0].record()
+        step()
+        ev[i][1].record()
+    torch.cuda.synchronize()
+    flash_attn_cuda.kernel_timing(False)
+    kt = flash_attn_cuda.kernel_timing_collect()
+    ms = sum(a.elapsed_time(b) for a, b in ev) / steps
+    # the same step replayed from a CUDA graph (dropout included: device-side Philox counter): what a training loop
+    # that graphs its step sees, free of the Python launch path
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        step()
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        step()
+    gev = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(steps)]
+    for i in range(steps):
+        if flush is not None:
+            flush.zero_()
+        gev[i][0].record()
+        graph.replay()
+        gev[i][1].record()
+    torch.cuda.synchronize()
+    gms = sum(a.elapsed_time(b) for a, b in gev) / steps
+    peaks = load_peaks()
+    kf, kb = kt["fwd_ms"] / max(kt["fwd_launches"], 1), kt["bwd_ms"] / max(kt["bwd_launches"], 1)
+    return {"workload": w["name"], "dtype": w["dtype"], "steps": steps, "ms_per_step": ms, "fwd_bwd_tflops": 3.5 * f_fwd / ms / 1e9,
+            "frac_of_bf16_burst_peak": 3.5 * f_fwd / ms / 1e9 / peaks["burst"],
+            "graph_ms_per_step": gms, "graph_fwd_bwd_tflops": 3.5 * f_fwd / gms / 1e9,
+            "fwd_kernel_ms": kf, "bwd_kernel_ms": kb, "fwd_kernel_tflops": f_fwd / kf / 1e9, "bwd_kernel_tflops": 2.5 * f_fwd / kb / 1e9,
+            "l2": "flushed between steps" if flush is not None else "inputs exceed L2"}
 
 
 def run_ours(args, w):
@@ -344,6 +453,29 @@ def run_ours(args, w):
     ms_step = times[0].item() / args.steps
     e2e_ms = times[1].item()
 
+    # what the host<->device path of this box delivers to this rank with nothing else on the GPU (all ranks copy at
+    # the same time): explains the end-to-end number, which is PCIe-bound
+    copy_gbs = []
+    for src, dst in ((qkv_h, qkv.detach()), (dqkv_h, qkv.detach())):
+        barrier()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record()
+        for _ in range(3):
+            if src is qkv_h:
+                dst.copy_(src, non_blocking=True)
+            else:
+                src.copy_(dst, non_blocking=True)
+        c1.record()
+        torch.cuda.synchronize()
+        copy_gbs.append(3 * qkv_h.numel() * qkv_h.element_size() / (c0.elapsed_time(c1) * 1e-3) / 1e9)
+    copy_t = torch.tensor(copy_gbs, device=device, dtype=torch.float64)
+    if dist is not None:
+        dist.all_reduce(copy_t, op=dist.ReduceOp.SUM)
+    # free the headline buffers before the other workloads
+    del qkv_dc, dout_dc, qkv_h, dout_h, out_h, dqkv_h
+    ring_rec = ring_record(args, WORKLOADS["ring64k"], world, rank, local_rank, device, dist, steps=max(3, min(args.steps, 5)),
+                           warmup=max(args.warmup, 3))
+
     if rank == 0:
         peaks = load_peaks()
         long_region = times[0].item() > 1000.0
@@ -364,7 +496,8 @@ def run_ours(args, w):
             pass
         value = world * f_step / (ms_step * 1e-3) / 1e12
         line = {
-            "metric": "attn fwd+bwd TFLOP/s per GPU", "value": value, "unit": "TFLOP/s", "n_gpus": world,
+            "metric": "attn fwd+bwd TFLOP/s, whole job (sum over the GPUs; per GPU: config.per_gpu_tflops)", "value": value,
+            "unit": "TFLOP/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": w["dtype"], "data": "synthetic",
             "config": {"workload": w["name"], "global_batch": w["b"] * world, "seq_len": s,
@@ -386,9 +519,14 @@ def run_ours(args, w):
                          "traffic": traffic},
             "e2e": {"value": world * f_step / (e2e_ms * 1e-3) / 1e12, "unit": "TFLOP/s", "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": in_bytes,
-                    "pipeline": f"{n_chunks} batch chunks; H2D, kernels and D2H on three streams"},
+                    "pipeline": f"{n_chunks} batch chunks; H2D, kernels and D2H on three streams",
+                    "host_link_gbs_all_ranks": {"h2d": copy_t[0].item(), "d2h": copy_t[1].item(),
+                                                "note": "pinned-memory copies alone, all ranks at once, summed over ranks"}},
             "gpu_launches": int(launches), "clocks": clocks,
+            "ring64k": ring_rec,
         }
+        if world == 1:
+            line["sub_records"] = {"d64_dropout": sub_record("d64", device), "bert_s512": sub_record("bert", device)}
         if world == 1 and not args.no_cpu_baseline:
             torch.set_num_threads(os.cpu_count() or 1)
             sb, sh = 1, 2

@@ -38,15 +38,12 @@ int check_device() {
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
-  static int cached_major[64];
-  static bool cached[64];
-  int major = 0;
-  if (dev < 64 && cached[dev]) {
-    major = cached_major[dev];
-  } else {
+  static std::atomic<int> cached_major[64];   // 0 = not queried yet; concurrent first calls just query twice
+  int major = dev < 64 ? cached_major[dev].load(std::memory_order_relaxed) : 0;
+  if (major == 0) {
     e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
     if (e != cudaSuccess) return cuda_fail(e, "cudaDeviceGetAttribute");
-    if (dev < 64) { cached_major[dev] = major; cached[dev] = true; }
+    if (dev < 64) cached_major[dev].store(major, std::memory_order_relaxed);
   }
   if (major != 10)
     return fail(FA_ERR_UNSUPPORTED_DEVICE, "libfa_b200 needs a compute capability 10.x (sm_100a) device, found %d.x", major);
@@ -96,6 +93,11 @@ int validate_common(const fa_params* p, bool bwd, bool block) {
                   t.name, (long long)t.rs, (long long)t.hs);
   }
   if (bwd && p->softmax_d == nullptr) return fail(FA_ERR_INVALID_ARGUMENT, "softmax_d is NULL");
+  if (p->flags & ~(FA_FLAG_WS_ZEROED)) return fail(FA_ERR_INVALID_ARGUMENT, "unknown flags 0x%x", p->flags);
+  if (p->alibi_slopes != nullptr && block)
+    return fail(FA_ERR_INVALID_ARGUMENT, "blocksparse attention does not take an attention bias");
+  if (p->impl == FA_IMPL_SIMT && (p->b > 65535 || p->h > 65535))
+    return fail(FA_ERR_INVALID_ARGUMENT, "the SIMT cross-check kernels support at most 65535 sequences / heads");
   if (block) {
     if (p->blockmask == nullptr) return fail(FA_ERR_INVALID_ARGUMENT, "blockmask is NULL");
     if (p->blockmask_nrow <= 0 || p->blockmask_ncol <= 0)
@@ -141,35 +143,42 @@ __global__ void scatter_rows_kernel(V* __restrict__ dst, const V* __restrict__ s
 // Ring / split-KV merge of two partial attention results over the same queries (the reference's inter-K-block rule,
 // src/fmha_fprop_kernel_1xN.h:606-650, lifted to whole blocks):
 //     lse' = log(exp(lse) + exp(lse_blk));   o' = o * exp(lse - lse') + o_blk * exp(lse_blk - lse')
-// o_acc fp32 (rows, h, d) contiguous, o_blk 16 bit (rows, h, d) contiguous; lse (b, h, stride) with rows = b * seqlen.
-// One thread per 8 head-dim elements; `first` = initialise the accumulator from the block.  The merged lse goes to a
-// second buffer (same shape as lse_acc; must not alias it) so that no thread can observe a half-updated row.
+// o_acc fp32 and o_blk 16 bit are (rows, h, d) contiguous with row = bi * batch_rows + t, t < seqlen (batch_rows >= seqlen
+// lets a call address one half of every sequence); lse_acc (b, h, acc_stride), lse_blk (b, h, blk_stride).  In place:
+// one thread per 8 head-dim elements, the d/8 threads of a (row, head) pair are padded to a power of two so that they
+// always sit in ONE warp -- all of them read lse_acc, the warp synchronises, then lane c8 = 0 overwrites it.
 template <bool kBf16>
-__global__ void __launch_bounds__(256) merge_partials_kernel(float* __restrict__ o_acc, const float* __restrict__ lse_acc, float* __restrict__ lse_out,
+__global__ void __launch_bounds__(256) merge_partials_kernel(float* __restrict__ o_acc, float* __restrict__ lse_acc,
                                                              const void* __restrict__ o_blk_, const float* __restrict__ lse_blk,
-                                                             int b, int h, int d, int seqlen, int acc_stride, int blk_stride,
-                                                             int first) {
+                                                             int b, int h, int d, int seqlen, int64_t batch_rows, int acc_stride,
+                                                             int blk_stride, int d8p, int first) {
   using T = typename Elem<kBf16>::T;
   const int d8 = d >> 3;
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const int64_t total = (int64_t)b * seqlen * h * d8;
-  if (idx >= total) return;
-  const int c8 = static_cast<int>(idx % d8);
-  const int hh = static_cast<int>((idx / d8) % h);
-  const int64_t row = idx / ((int64_t)d8 * h);
-  const int bi = static_cast<int>(row / seqlen), t = static_cast<int>(row % seqlen);
+  const int64_t total = (int64_t)b * seqlen * h * d8p;
+  const bool in_range = idx < total;
+  const int c8 = static_cast<int>(idx % d8p);
+  const int hh = static_cast<int>((idx / d8p) % h);
+  const int64_t row = idx / ((int64_t)d8p * h);
+  const int bi = in_range ? static_cast<int>(row / seqlen) : 0, t = in_range ? static_cast<int>(row % seqlen) : 0;
   const int64_t ia = ((int64_t)bi * h + hh) * acc_stride + t, ib = ((int64_t)bi * h + hh) * blk_stride + t;
-  const float lb = lse_blk[ib];
-  const float la = first ? -INFINITY : lse_acc[ia];
-  const float mx = fmaxf(la, lb);
   float wa = 0.f, wb = 0.f, ln = -INFINITY;
-  if (mx != -INFINITY) {
-    const float ea = __expf(la - mx), eb = __expf(lb - mx);
-    ln = mx + __logf(ea + eb);
-    wa = ea / (ea + eb);
-    wb = eb / (ea + eb);
+  if (in_range) {
+    const float lb = lse_blk[ib];
+    const float la = first ? -INFINITY : lse_acc[ia];
+    const float mx = fmaxf(la, lb);
+    if (mx != -INFINITY) {
+      const float ea = __expf(la - mx), eb = __expf(lb - mx);
+      ln = mx + __logf(ea + eb);
+      wa = ea / (ea + eb);
+      wb = eb / (ea + eb);
+    }
   }
-  const int64_t off = (row * h + hh) * d + c8 * 8;
+  __syncwarp();
+  if (!in_range) return;
+  if (c8 == 0) lse_acc[ia] = ln;
+  if (c8 >= d8) return;
+  const int64_t off = (((int64_t)bi * batch_rows + t) * h + hh) * d + c8 * 8;
   const uint4 raw = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(o_blk_) + off));
   const T* e = reinterpret_cast<const T*>(&raw);
   float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
@@ -187,7 +196,34 @@ __global__ void __launch_bounds__(256) merge_partials_kernel(float* __restrict__
   a1.w = a1.w * wa + Elem<kBf16>::to_float(e[7]) * wb;
   *reinterpret_cast<float4*>(o_acc + off) = a0;
   *reinterpret_cast<float4*>(o_acc + off + 4) = a1;
-  if (c8 == 0) lse_out[ia] = ln;   // separate buffer: the other threads of this (row, head) still read lse_acc
+}
+
+// dst (fp32) += src (16 bit) over n_batches runs of run_elems contiguous elements (run_elems % 8 == 0): the ring backward
+// adds each step's dQ / dK / dV block into its fp32 accumulators.  HBM-bound, 8 elements per thread, grid-stride.
+template <bool kBf16>
+__global__ void __launch_bounds__(256) accumulate_f32_kernel(float* __restrict__ dst, const void* __restrict__ src_, int64_t n_batches,
+                                                             int64_t run_elems, int64_t dst_batch_stride, int64_t src_batch_stride) {
+  using T = typename Elem<kBf16>::T;
+  const int64_t run8 = run_elems >> 3, total = n_batches * run8;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t bi = idx / run8, e8 = idx - bi * run8;
+    const uint4 raw = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(src_) + bi * src_batch_stride + e8 * 8));
+    const T* e = reinterpret_cast<const T*>(&raw);
+    float4* d4 = reinterpret_cast<float4*>(dst + bi * dst_batch_stride + e8 * 8);
+    float4 a0 = d4[0], a1 = d4[1];
+    a0.x += Elem<kBf16>::to_float(e[0]); a0.y += Elem<kBf16>::to_float(e[1]);
+    a0.z += Elem<kBf16>::to_float(e[2]); a0.w += Elem<kBf16>::to_float(e[3]);
+    a1.x += Elem<kBf16>::to_float(e[4]); a1.y += Elem<kBf16>::to_float(e[5]);
+    a1.z += Elem<kBf16>::to_float(e[6]); a1.w += Elem<kBf16>::to_float(e[7]);
+    d4[0] = a0;
+    d4[1] = a1;
+  }
+}
+
+__global__ void philox_advance_kernel(uint64_t* state, uint64_t* out, uint64_t increment) {
+  const uint64_t v = *state;
+  *out = v;
+  *state = v + increment;
 }
 
 // Rotary position embedding applied to the first `n_rot` parts (q, k) of a packed (rows, n_parts, h, d) tensor in ONE
@@ -395,6 +431,26 @@ uint64_t fa_workspace_bytes(const fa_params* p, int op) {
   return bytes;
 }
 
+uint64_t fa_workspace_zero_range(const fa_params* p, int op, uint64_t* begin) {
+  uint64_t off = 0, len = 0;
+  if (p != nullptr) {
+    if (op == FA_OP_FWD_BLOCK || op == FA_OP_BWD_BLOCK) off = fa::blockmask_bytes(p);
+    if ((op == FA_OP_BWD || op == FA_OP_BWD_BLOCK) && p->impl != FA_IMPL_SIMT) len = fa::bwd_sm100_workspace_zero_bytes(*p);
+  }
+  if (begin != nullptr) *begin = off;
+  return len;
+}
+
+int fa_philox_advance(uint64_t* state, uint64_t* out, uint64_t increment, void* stream) {
+  fa::g_last_error[0] = 0;
+  if (state == nullptr || out == nullptr) return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_philox_advance: NULL pointer");
+  fa::philox_advance_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(state, out, increment);
+  fa::count_launch();
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fa::cuda_fail(e, "philox_advance launch");
+  return FA_OK;
+}
+
 // The dropout stream is keyed by position, so one call consumes one "slot" of the generator; the increment is
 // kept a multiple of 4 like ATen's philox_cuda_state (fmha_api.cpp:228-234).
 uint64_t fa_philox_increment(const fa_params* p) { return (p != nullptr && p->p_dropout > 0.f) ? 4 : 0; }
@@ -427,25 +483,49 @@ int fa_bwd(const fa_params* p, void* stream) { return fa::run_bwd(p, stream, fal
 int fa_fwd_block(const fa_params* p, void* stream) { return fa::run_fwd(p, stream, true); }
 int fa_bwd_block(const fa_params* p, void* stream) { return fa::run_bwd(p, stream, true); }
 
-int fa_merge_partials(float* o_acc, const float* lse_acc, float* lse_out, const void* o_blk, const float* lse_blk, int32_t b, int32_t h, int32_t d,
-                      int32_t seqlen, int32_t lse_acc_stride, int32_t lse_blk_stride, int32_t is_bf16, int32_t first,
-                      void* stream) {
+int fa_merge_partials(float* o_acc, float* lse_acc, const void* o_blk, const float* lse_blk, int32_t b, int32_t h, int32_t d,
+                      int32_t seqlen, int64_t batch_rows, int32_t lse_acc_stride, int32_t lse_blk_stride, int32_t is_bf16,
+                      int32_t first, void* stream) {
   fa::g_last_error[0] = 0;
-  if (b <= 0 || h <= 0 || seqlen < 0 || d <= 0 || d % 8 != 0)
+  if (b <= 0 || h <= 0 || seqlen < 0 || d <= 0 || d % 8 != 0 || d > 128)
     return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_merge_partials: bad sizes (b %d, h %d, d %d, seqlen %d)", b, h, d, seqlen);
   if (seqlen == 0) return FA_OK;
-  if (!o_acc || !lse_acc || !lse_out || lse_out == lse_acc || !o_blk || !lse_blk) return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_merge_partials: NULL or aliased pointer");
-  if (lse_acc_stride < seqlen || lse_blk_stride < seqlen) return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_merge_partials: lse stride < seqlen");
+  if (!o_acc || !lse_acc || !o_blk || !lse_blk) return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_merge_partials: NULL pointer");
+  if (lse_acc_stride < seqlen || lse_blk_stride < seqlen || batch_rows < seqlen)
+    return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_merge_partials: lse stride or batch_rows < seqlen");
   int rc = fa::check_device();
   if (rc != FA_OK) return rc;
-  const int64_t total = (int64_t)b * seqlen * h * (d / 8);
+  int d8p = 1;
+  while (d8p < d / 8) d8p *= 2;
+  const int64_t total = (int64_t)b * seqlen * h * d8p;
   const unsigned grid = static_cast<unsigned>((total + 255) / 256);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (is_bf16) fa::merge_partials_kernel<true><<<grid, 256, 0, st>>>(o_acc, lse_acc, lse_out, o_blk, lse_blk, b, h, d, seqlen, lse_acc_stride, lse_blk_stride, first);
-  else fa::merge_partials_kernel<false><<<grid, 256, 0, st>>>(o_acc, lse_acc, lse_out, o_blk, lse_blk, b, h, d, seqlen, lse_acc_stride, lse_blk_stride, first);
+  if (is_bf16) fa::merge_partials_kernel<true><<<grid, 256, 0, st>>>(o_acc, lse_acc, o_blk, lse_blk, b, h, d, seqlen, batch_rows, lse_acc_stride, lse_blk_stride, d8p, first);
+  else fa::merge_partials_kernel<false><<<grid, 256, 0, st>>>(o_acc, lse_acc, o_blk, lse_blk, b, h, d, seqlen, batch_rows, lse_acc_stride, lse_blk_stride, d8p, first);
   fa::count_launch();
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fa::cuda_fail(e, "merge_partials launch");
+  return FA_OK;
+}
+
+int fa_accumulate_f32(float* dst, const void* src, int64_t n_batches, int64_t run_elems, int64_t dst_batch_stride,
+                      int64_t src_batch_stride, int32_t is_bf16, void* stream) {
+  fa::g_last_error[0] = 0;
+  if (n_batches < 0 || run_elems < 0 || run_elems % 8 != 0 || dst_batch_stride % 4 != 0 || src_batch_stride % 8 != 0)
+    return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_accumulate_f32: sizes and strides must be multiples of 8 elements");
+  if (n_batches == 0 || run_elems == 0) return FA_OK;
+  if (!dst || !src || !fa::aligned16(dst) || !fa::aligned16(src))
+    return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_accumulate_f32: NULL or misaligned pointer");
+  int rc = fa::check_device();
+  if (rc != FA_OK) return rc;
+  const int64_t want = (n_batches * (run_elems / 8) + 255) / 256;
+  const unsigned grid = static_cast<unsigned>(want < 148 * 16 ? want : 148 * 16);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (is_bf16) fa::accumulate_f32_kernel<true><<<grid, 256, 0, st>>>(dst, src, n_batches, run_elems, dst_batch_stride, src_batch_stride);
+  else fa::accumulate_f32_kernel<false><<<grid, 256, 0, st>>>(dst, src, n_batches, run_elems, dst_batch_stride, src_batch_stride);
+  fa::count_launch();
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fa::cuda_fail(e, "accumulate_f32 launch");
   return FA_OK;
 }
 
@@ -493,7 +573,7 @@ int fa_rotary_qk(const void* in, void* out, const float* cos_t, const float* sin
 void fa_dropout_keep8_host(uint64_t seed, uint64_t offset, uint32_t bh, uint32_t qrow, uint32_t kgroup, float p_dropout,
                            uint8_t* keep) {
   const fa::PhiloxKey pk = fa::make_philox_key(seed, offset);
-  const uint4 r = fa::dropout_rand8(pk, bh, qrow, kgroup);
+  const uint4 r = fa::dropout_rand8(pk, pk.c3, bh, qrow, kgroup);
   const uint32_t thr = fa::keep_threshold_u16(p_dropout);
   for (int e = 0; e < 8; ++e) keep[e] = fa::rand8_get(r, e) <= thr ? 1 : 0;
 }

@@ -5,7 +5,10 @@
 //     P = exp(scale*S - lse)   dV = (P o Z / keep)^T dO   dP = (dO V^T) o Z / keep   dS = P o (dP - D)
 //     D = rowsum(dO o O)       dQ = scale * dS K          dK = scale * dS^T Q
 //
-// Three launches:  preprocess (D, -lse*log2e, per row)  ->  main  ->  postprocess (dQ fp32 accumulator -> 16 bit).
+// Two launches:  preprocess (D, -lse*log2e, per row)  ->  main.  The fp32 dQ accumulator is converted to 16 bit inside the
+// main kernel by whichever CTA adds the last contribution to a query tile (a counter per tile quarter); that CTA also
+// writes zeros back, so the accumulator is clean for the next call and needs neither a memset nor a postprocess pass.
+// (The blocksparse variant, whose contributor count per tile depends on the mask, keeps the separate postprocess launch.)
 //
 // Main kernel: one CTA owns a block of 128 keys (K and V tiles stay in shared memory) and streams 128-row Q / dO tiles.
 // Everything the softmax-side threads touch is computed TRANSPOSED (keys on TMEM lanes, queries on TMEM columns):
@@ -16,8 +19,10 @@
 // cp.reduce.async.bulk (one 8 KB bulk reduction per 16 head-dim columns); the postprocess kernel scales and converts it.
 // TMEM columns: S^T/P^T [0,128) | dP^T, then dQ [128,256) | dV [256,256+DPAD) | dK [384,384+DPAD).
 // Warps: 0-7 compute (warpgroup g handles query columns 64g..64g+63 of every tile), 8-11 dQ drain, 12 MMA issuer,
-// 13 TMA loader, 14-15 idle.
+// 13 TMA loader, 14 dQ finaliser (accumulator -> 16-bit dq for completed tiles), 15 zero-fill of rows beyond a sequence.
 #include <cudaTypedefs.h>
+
+#include <atomic>
 
 #include "fa_common.cuh"
 #include "fa_kernels.h"
@@ -53,9 +58,11 @@ struct BwdSmem {
   static constexpr int kMaskOff = kStatOff + kQStages * 1024;    // dropout keep bits: 2 x [4 key words][128 queries] u32
   static constexpr int kListOff = kMaskOff + 2 * 2048;    // blocksparse: int16 list[512], uint8 flags[512]
   static constexpr int kBarOff = kListOff + kMaxSparseTiles * 3;
-  static constexpr int kNumBars = 18;
+  static constexpr int kNumBars = 21;                     // + k_fix, q_fix, do_fix
   static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
-  static constexpr int kTotal = kTmemPtrOff + 16;
+  static constexpr int kFinQueueOff = kTmemPtrOff + 16;   // dQ finaliser queue: tail, head, drains done, pad, entries[kFinQueue]
+  static constexpr int kFinQueue = 64;
+  static constexpr int kTotal = kFinQueueOff + 16 + kFinQueue * 4;
   static constexpr int kDynamicBytes = kTotal + 1024;     // + alignment slack
 };
 static_assert(BwdSmem<128>::kDynamicBytes <= 232448, "shared memory budget");
@@ -64,12 +71,17 @@ struct BwdTensorMaps {
   CUtensorMap q, k, v, dout;
 };
 
+// Backward scratch, indexed by PACKED row so that it is O(total_q * h * d) whatever the batch looks like: sequence b owns the
+// 128-row tile slots  (q_begin >> 7) + b + m,  m = 0 .. ceil(seqlen_q / 128) - 1  (slots of different sequences never overlap,
+// and there are at most (total_q >> 7) + b + 1 of them).
 struct BwdWs {
-  float* nl;         // (b*h, sq_pad): -lse*log2e, -inf for rows that must produce P = 0
-  float* dsum;       // (b*h, sq_pad): D = rowsum(dO o O), 0 for invalid rows
-  float* dq_accum;   // (b*h, n_qtiles, 4 row quarters, DPAD/4, 32, 4) fp32
-  int sq_pad, n_qtiles;
+  float* nl;         // (h, n_slots * 128): -lse*log2e, -inf for rows that must produce P = 0
+  float* dsum;       // (h, n_slots * 128): D = rowsum(dO o O), 0 for invalid rows
+  float* dq_accum;   // (h, n_slots, 4 row quarters, DPAD/4, 32, 4) fp32; all zero on entry and on exit
+  uint32_t* dq_count;   // (h, n_slots, 4): contributions received per tile quarter; all zero on entry and on exit
+  int n_slots;
 };
+__device__ __forceinline__ int tile_slot(int q_begin, int bidb, int m) { return (q_begin >> 7) + bidb + m; }
 
 // Optional timeline tracing of one CTA (build with -DFA_BWD_TRACE; tools/trace_bwd.py): clock64 at pipeline events.
 #ifdef FA_BWD_TRACE
@@ -98,10 +110,45 @@ __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
+// dQ finalisation of one tile quarter (32 query rows): fp32 accumulator (L2) -> x scale -> 16 bit -> dq, and zeros written
+// back so that the accumulator is clean for the next call.  Quarter layout: [DPAD/16 chunks][4 column groups][32 rows][4].
+// `dq_row`: this lane's output row, nullptr when the row lies beyond the sequence.  kBatch chunks are in flight at a time.
+template <int DPAD, bool kBf16, int kBatch>
+__device__ __forceinline__ void finalize_dq_quarter(float* acc, uint16_t* dq_row, int d, float scale, int lane) {
+  constexpr int kChunks = DPAD / 16;
+#pragma unroll 1
+  for (int k0 = 0; k0 < kChunks; k0 += kBatch) {
+    float4 v[kBatch][4];
+#pragma unroll
+    for (int b = 0; b < kBatch; ++b)
+#pragma unroll
+      for (int g = 0; g < 4; ++g) v[b][g] = __ldcg(reinterpret_cast<const float4*>(acc + (k0 + b) * 512 + g * 128 + lane * 4));
+#pragma unroll
+    for (int b = 0; b < kBatch; ++b)
+#pragma unroll
+      for (int g = 0; g < 4; ++g) __stcg(reinterpret_cast<float4*>(acc + (k0 + b) * 512 + g * 128 + lane * 4), make_float4(0.f, 0.f, 0.f, 0.f));
+#pragma unroll
+    for (int b = 0; b < kBatch; ++b) {
+      const int col = (k0 + b) * 16;
+      uint4 lo, hi;
+      lo.x = pack2<kBf16>(v[b][0].x * scale, v[b][0].y * scale);
+      lo.y = pack2<kBf16>(v[b][0].z * scale, v[b][0].w * scale);
+      lo.z = pack2<kBf16>(v[b][1].x * scale, v[b][1].y * scale);
+      lo.w = pack2<kBf16>(v[b][1].z * scale, v[b][1].w * scale);
+      hi.x = pack2<kBf16>(v[b][2].x * scale, v[b][2].y * scale);
+      hi.y = pack2<kBf16>(v[b][2].z * scale, v[b][2].w * scale);
+      hi.z = pack2<kBf16>(v[b][3].x * scale, v[b][3].y * scale);
+      hi.w = pack2<kBf16>(v[b][3].z * scale, v[b][3].w * scale);
+      if (dq_row != nullptr && col < d) *reinterpret_cast<uint4*>(dq_row + col) = lo;
+      if (dq_row != nullptr && col + 8 < d) *reinterpret_cast<uint4*>(dq_row + col + 8) = hi;
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // main kernel
 // ------------------------------------------------------------------------------------------------
-template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse>
+template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse, bool kAlibi>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, const BlockMaskView bm, const BwdWs ws,
                  const int n_kblocks, const int bh_group, const PhiloxKey pk) {   // round keys precomputed on the host (constant bank)
@@ -110,7 +157,8 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // causal: 1-D launch, longest (lowest key block) first within groups of (batch, head) pairs; else grid (block, h, b)
+  // 1-D launch.  causal: longest (lowest key block) first within groups of (batch, head) pairs; else block-major inside
+  // each (batch, head) pair
   int bidb, bidh, n_blk;
   if (kCausal) {
     const CtaCoord c = decode_cta(blockIdx.x, n_kblocks, p.b * p.h, bh_group);
@@ -118,9 +166,12 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     bidb = c.bh / p.h;
     bidh = c.bh - bidb * p.h;
   } else {
-    bidb = blockIdx.z, bidh = blockIdx.y, n_blk = blockIdx.x;
+    const int pair = blockIdx.x / n_kblocks;
+    n_blk = blockIdx.x - pair * n_kblocks;
+    bidb = pair / p.h;
+    bidh = pair - bidb * p.h;
   }
-  const SeqInfo seq(p.cu_seqlens_q, p.cu_seqlens_k, bidb);
+  const SeqInfo seq(p, bidb);
   const int k0 = n_blk * kBN;
 #ifdef FA_BWD_TRACE
   if (threadIdx.x == 0) {
@@ -153,6 +204,12 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
   uint64_t* dq_full = bars + 15;
   uint64_t* dq_empty = bars + 16;
   uint64_t* dkv_full = bars + 17;
+  // landing barriers of tiles that reach past their sequence: the TMA completes on these, warp 15 zeroes the stray rows
+  // and only then completes k_full / q_full[s] / do_full for the MMA warp
+  uint64_t* k_fix = bars + 18;
+  uint64_t* q_fix = bars + 19;
+  uint64_t* do_fix = bars + 20;
+  volatile uint32_t* fin_q = reinterpret_cast<volatile uint32_t*>(smem + L::kFinQueueOff);   // [0] tail [1] head [2] drains done
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + L::kTmemPtrOff);
   int16_t* tile_list = reinterpret_cast<int16_t*>(smem + L::kListOff);
   uint8_t* tile_flags = smem + L::kListOff + kMaxSparseTiles * 2;
@@ -192,6 +249,16 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     n_iter = s_num_active;
   }
   auto tile_of = [&](int it) -> int { return kSparse ? static_cast<int>(tile_list[it]) : m_start + it; };
+  // Isolation of sequences (the reference predicates its loads on row < seqlen and zero-fills): tiles that reach past the
+  // sequence hold the next sequence's rows or whatever lies behind the packed batch.  The softmax-side threads mask such
+  // entries with selects, but the MMAs would still multiply an exact 0 by a stray NaN: dQ = dS K (stray K rows),
+  // dK = dS^T Q and dV = P^T dO (stray rows of the last query tile).  Warp 15 zeroes those rows in shared memory.
+  const int k_valid = seq.seqlen_k - k0;                 // valid key rows of this block (>= 1)
+  const bool kv_partial = k_valid < kBN;
+  const int q_valid_last = seq.seqlen_q - (n_qt_total - 1) * kBM;   // valid rows of the last query tile (1..128)
+  const bool q_partial = n_iter > 0 && q_valid_last < kBM && tile_of(n_iter - 1) == n_qt_total - 1;   // then it is the last iteration
+  constexpr bool kFusedDq = !kSparse;                    // dQ finalised in-kernel (see the drain / finaliser warps)
+  const int slot0 = tile_slot(seq.q_begin, bidb, 0);
 
   uint8_t* sK = smem + L::kKOff;
   uint8_t* sV = smem + L::kVOff;
@@ -209,30 +276,37 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     }
     mbar_init(do_full, 1);
     mbar_init(do_empty, 1);
+    mbar_init(k_fix, 1);
+    mbar_init(q_fix, 1);
+    mbar_init(do_fix, 1);
     fence_mbar_init();
     tma_prefetch_desc(&maps.q);
     tma_prefetch_desc(&maps.k);
     tma_prefetch_desc(&maps.v);
     tma_prefetch_desc(&maps.dout);
     if (n_iter > 0) {   // nobody waits for K / V otherwise, and a CTA must not exit with loads in flight
-      mbar_arrive_expect_tx(k_full, L::kTile);
+      uint64_t* kbar = kv_partial ? k_fix : k_full;
+      mbar_arrive_expect_tx(kbar, L::kTile);
 #pragma unroll
-      for (int c = 0; c < DPAD / 64; ++c) tma_load_3d(sK + c * L::kSub, &maps.k, k_full, c * 64, bidh, seq.k_begin + k0);
+      for (int c = 0; c < DPAD / 64; ++c) tma_load_3d(sK + c * L::kSub, &maps.k, kbar, c * 64, bidh, seq.k_begin + k0);
       const int m = tile_of(0);
-      mbar_arrive_expect_tx(&q_full[0], L::kTile + 1024);
+      const bool fix0 = q_partial && n_iter == 1;
+      uint64_t* qbar = fix0 ? q_fix : &q_full[0];
+      mbar_arrive_expect_tx(qbar, L::kTile + 1024);
 #pragma unroll
       for (int c = 0; c < DPAD / 64; ++c)
-        tma_load_3d(sQ + c * L::kSub, &maps.q, &q_full[0], c * 64, bidh, seq.q_begin + m * kBM);
-      const int64_t stat_off = (int64_t)bh * ws.sq_pad + m * kBM;
-      bulk_load_1d(sStat, ws.nl + stat_off, 512, &q_full[0]);
-      bulk_load_1d(sStat + 128, ws.dsum + stat_off, 512, &q_full[0]);
+        tma_load_3d(sQ + c * L::kSub, &maps.q, qbar, c * 64, bidh, seq.q_begin + m * kBM);
+      const int64_t stat_off = ((int64_t)bidh * ws.n_slots + slot0 + m) * kBM;
+      bulk_load_1d(sStat, ws.nl + stat_off, 512, qbar);
+      bulk_load_1d(sStat + 128, ws.dsum + stat_off, 512, qbar);
       mbar_arrive_expect_tx(v_full, L::kTile);
 #pragma unroll
       for (int c = 0; c < DPAD / 64; ++c) tma_load_3d(sV + c * L::kSub, &maps.v, v_full, c * 64, bidh, seq.k_begin + k0);
-      mbar_arrive_expect_tx(do_full, L::kTile);
+      uint64_t* dobar = fix0 ? do_fix : do_full;
+      mbar_arrive_expect_tx(dobar, L::kTile);
 #pragma unroll
       for (int c = 0; c < DPAD / 64; ++c)
-        tma_load_3d(sDo + c * L::kSub, &maps.dout, do_full, c * 64, bidh, seq.q_begin + m * kBM);
+        tma_load_3d(sDo + c * L::kSub, &maps.dout, dobar, c * 64, bidh, seq.q_begin + m * kBM);
     }
   }
   __syncwarp();
@@ -245,8 +319,10 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     mbar_init(dq_full, 1);
     mbar_init(dq_empty, 128);
     mbar_init(dkv_full, 1);
+    fin_q[0] = 0; fin_q[1] = 0; fin_q[2] = 0;
     fence_mbar_init();
   }
+  if (threadIdx.x >= 64 && threadIdx.x < 64 + L::kFinQueue) fin_q[4 + threadIdx.x - 64] = 0xFFFFFFFFu;   // empty slot
   if (warp == 0) {
     tmem_alloc(tmem_ptr_smem, 512);
     tmem_relinquish();
@@ -256,6 +332,13 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
   if (threadIdx.x == 0) FA_CTA_MARK(3, clock64());
+  // dQ tile (b, m) is complete when every key-block CTA that visits it has added its partial
+  const int nkb_seq = (seq.seqlen_k + kBN - 1) / kBN;
+  auto dq_contributors = [&](int m) -> uint32_t { return static_cast<uint32_t>(kCausal ? min(m + 1, nkb_seq) : nkb_seq); };
+  auto dq_row_ptr = [&](int row) -> uint16_t* {   // row within the sequence
+    return row < seq.seqlen_q ? reinterpret_cast<uint16_t*>(p.dq) + (int64_t)(seq.q_begin + row) * p.dq_row_stride + (int64_t)bidh * p.dq_head_stride
+                              : nullptr;
+  };
 
   uint8_t* sDs = smem + L::kDsOff;
   uint8_t* sDq = smem + L::kDqOff;
@@ -276,21 +359,24 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
         for (int it = 1; it < n_iter; ++it) {
           const int m = tile_of(it);
           const int s = it % kQ;
+          const bool fix = q_partial && it + 1 == n_iter;
           mbar_wait(&q_empty[s], ((it / kQ) & 1) ^ 1);
           FA_TRACE(20);
-          mbar_arrive_expect_tx(&q_full[s], L::kTile + 1024);
+          uint64_t* qbar = fix ? q_fix : &q_full[s];
+          mbar_arrive_expect_tx(qbar, L::kTile + 1024);
 #pragma unroll
           for (int c = 0; c < DPAD / 64; ++c)
-            tma_load_3d(sQ + s * L::kTile + c * L::kSub, &maps.q, &q_full[s], c * 64, bidh, seq.q_begin + m * kBM);
-          const int64_t stat_off = (int64_t)bh * ws.sq_pad + m * kBM;
-          bulk_load_1d(sStat + s * 256, ws.nl + stat_off, 512, &q_full[s]);
-          bulk_load_1d(sStat + s * 256 + 128, ws.dsum + stat_off, 512, &q_full[s]);
+            tma_load_3d(sQ + s * L::kTile + c * L::kSub, &maps.q, qbar, c * 64, bidh, seq.q_begin + m * kBM);
+          const int64_t stat_off = ((int64_t)bidh * ws.n_slots + slot0 + m) * kBM;
+          bulk_load_1d(sStat + s * 256, ws.nl + stat_off, 512, qbar);
+          bulk_load_1d(sStat + s * 256 + 128, ws.dsum + stat_off, 512, qbar);
           mbar_wait(do_empty, (it & 1) ^ 1);
           FA_TRACE(21);
-          mbar_arrive_expect_tx(do_full, L::kTile);
+          uint64_t* dobar = fix ? do_fix : do_full;
+          mbar_arrive_expect_tx(dobar, L::kTile);
 #pragma unroll
           for (int c = 0; c < DPAD / 64; ++c)
-            tma_load_3d(sDo + c * L::kSub, &maps.dout, do_full, c * 64, bidh, seq.q_begin + m * kBM);
+            tma_load_3d(sDo + c * L::kSub, &maps.dout, dobar, c * 64, bidh, seq.q_begin + m * kBM);
         }
       }
     } else if (warp == 12) {
@@ -443,6 +529,65 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
         commit(dkv_full);
       }
       __syncwarp();
+    } else if (warp == 15) {
+      // ===================================== zero-fill of stray rows ===========================
+      auto zero_rows = [&](uint32_t tile_addr, int first_row) {   // rows [first_row, 128) of every 64-column sub tile
+        const int n16 = (128 - first_row) * 8;                    // 128-byte rows; the swizzle stays inside a row
+        for (int idx = lane; idx < n16 * (DPAD / 64); idx += 32) {
+          const int sub = idx / n16, r = idx - sub * n16;
+          st_shared_v4(tile_addr + sub * L::kSub + first_row * 128 + r * 16, 0u, 0u, 0u, 0u);
+        }
+        fence_proxy_async();
+        __syncwarp();
+      };
+      if (n_iter > 0 && kv_partial) {
+        mbar_wait(k_fix, 0);
+        zero_rows(smem_u32(sK), k_valid);
+        if (lane == 0) mbar_arrive(k_full);
+      }
+      if (q_partial) {
+        const int s = (n_iter - 1) % kQ;
+        mbar_wait(q_fix, 0);
+        zero_rows(smem_u32(sQ) + s * L::kTile, q_valid_last);
+        if (lane == 0) mbar_arrive(&q_full[s]);
+        mbar_wait(do_fix, 0);
+        zero_rows(smem_u32(sDo), q_valid_last);
+        if (lane == 0) mbar_arrive(do_full);
+      }
+    } else {
+      // ===================================== dQ finaliser (warp 14) ============================
+      // Tile quarters whose last contribution came from this CTA (queued by the drain warps) are converted here, off
+      // the drain warps' critical path: accumulator (L2) -> dq, zeros written back.
+      if constexpr (kFusedDq) {
+        uint32_t head = 0;
+        uint64_t idle_since = 0;               // like mbar_wait: a protocol bug traps instead of hanging the GPU
+        while (true) {
+          const uint32_t done = fin_q[2];      // read before the tail: a drain warp queues before it reports done
+          const uint32_t tail = fin_q[0];
+          if (head == tail) {
+            if (done == 4) break;
+            __nanosleep(200);
+            const uint64_t now = global_timer_ns();
+            if (idle_since == 0) idle_since = now;
+            else if (now - idle_since > 4 * FA_WAIT_TIMEOUT_NS) { asm volatile("trap;\n"); }
+            continue;
+          }
+          idle_since = 0;
+          uint32_t e;
+          while ((e = fin_q[4 + head % L::kFinQueue]) == 0xFFFFFFFFu) __nanosleep(32);
+          __threadfence();                     // acquire side of the drain warp's counter update
+          const int m = static_cast<int>(e >> 2), q4 = static_cast<int>(e & 3u);
+          float* acc = ws.dq_accum + ((int64_t)bidh * ws.n_slots + slot0 + m) * (kBM * DPAD) + q4 * (32 * DPAD);
+          finalize_dq_quarter<DPAD, kBf16, 2>(acc, dq_row_ptr(m * kBM + q4 * 32 + lane), p.d, p.softmax_scale, lane);
+          __syncwarp();
+          if (lane == 0) {
+            fin_q[4 + head % L::kFinQueue] = 0xFFFFFFFFu;
+            __threadfence_block();
+            fin_q[1] = head + 1;
+          }
+          ++head;
+        }
+      }
     }
   } else if (warp >= 8) {
     // ===================================== dQ drain warps ======================================
@@ -457,9 +602,39 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     constexpr int kChunks = DPAD / 16;
     constexpr int kRing = kChunks < 8 ? kChunks : 8;
     uint32_t n_issued = 0;
+    // Completion protocol (kFusedDq): once the reductions of a tile have COMPLETED (bulk wait_group without .read), the
+    // warp bumps the tile quarter's counter; the warp that brings it to the number of contributing key blocks owns the
+    // finished sum.  Tile it-1 is signalled after tile it has been issued, so the wait never stalls the drain; the
+    // conversion goes to the finaliser warp's queue, except for the CTA's last tile, which this warp converts itself.
+    auto signal_tile = [&](int m_done, bool last_tile) {
+      uint32_t is_last = 0;
+      if (lane == 0) {
+        if (last_tile) bulk_wait_group<0>(); else bulk_wait_group<kChunks>();
+        __threadfence();
+        uint32_t* cnt = ws.dq_count + ((int64_t)bidh * ws.n_slots + slot0 + m_done) * 4 + wq;
+        const uint32_t old = atomicAdd(cnt, 1u);
+        if (old + 1 == dq_contributors(m_done)) {
+          is_last = 1;
+          __threadfence();
+          *cnt = 0;                           // clean for the next call
+        }
+      }
+      is_last = __shfl_sync(0xffffffffu, is_last, 0);
+      if (is_last) {
+        if (last_tile) {
+          float* acc = ws.dq_accum + ((int64_t)bidh * ws.n_slots + slot0 + m_done) * (kBM * DPAD) + wq * (32 * DPAD);
+          finalize_dq_quarter<DPAD, kBf16, 4>(acc, dq_row_ptr(m_done * kBM + wq * 32 + lane), p.d, p.softmax_scale, lane);
+        } else if (lane == 0) {
+          uint32_t* q32 = const_cast<uint32_t*>(fin_q);
+          const uint32_t idx = atomicAdd(q32, 1u);
+          while (idx - fin_q[1] >= static_cast<uint32_t>(L::kFinQueue)) __nanosleep(64);   // queue full: wait for the finaliser
+          fin_q[4 + idx % L::kFinQueue] = (static_cast<uint32_t>(m_done) << 2) | static_cast<uint32_t>(wq);
+        }
+      }
+    };
     for (int it = 0; it < n_iter; ++it) {
       const int m = tile_of(it);
-      float* gdst = ws.dq_accum + ((int64_t)bh * ws.n_qtiles + m) * (kBM * DPAD) + wq * (32 * DPAD);
+      float* gdst = ws.dq_accum + ((int64_t)bidh * ws.n_slots + slot0 + m) * (kBM * DPAD) + wq * (32 * DPAD);
       mbar_wait(dq_full, it & 1);
       if (wq == 0) FA_TRACE(16);
       tc_fence_after();
@@ -505,9 +680,19 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
         }
       }
       if (wq == 0) FA_TRACE(18);
+      if (kFusedDq && it > 0) signal_tile(tile_of(it - 1), false);
     }
     if (warp == 8 && lane == 0) FA_CTA_MARK(9, clock64());    // last chunk issued
-    if (lane == 0) bulk_wait_group_read<0>();   // the staging buffers may go away; the reductions complete on their own
+    if constexpr (kFusedDq) {
+      if (n_iter > 0) signal_tile(tile_of(n_iter - 1), true);
+      __syncwarp();
+      if (lane == 0) {
+        __threadfence_block();
+        atomicAdd(const_cast<uint32_t*>(fin_q) + 2, 1u);   // this drain warp has queued everything it ever will
+      }
+    } else {
+      if (lane == 0) bulk_wait_group_read<0>();   // the staging buffers may go away; the reductions complete on their own
+    }
     if (warp == 8 && lane == 0) FA_CTA_MARK(10, clock64());
   } else {
     // ===================================== compute warps =======================================
@@ -517,7 +702,6 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     const int kl = wq * 32 + lane;      // key row within the block (= TMEM lane)
     const int key = k0 + kl;
     const bool key_valid = key < seq.seqlen_k;
-    const bool kv_partial = k0 + kBN > seq.seqlen_k;
     const uint32_t lane_base = static_cast<uint32_t>(wq * 32) << 16;
     const uint32_t tS = tmem_base + lane_base + kColS + g * 64;
     const uint32_t tDP = tmem_base + lane_base + kColDP + g * 64;
@@ -525,6 +709,8 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     const float rp_dropout = 1.f / (1.f - p.p_dropout);
     const uint32_t keep_thr = keep_threshold_u16(p.p_dropout);
     const uint32_t keep_thr_hi = (keep_thr << 16) | 0xFFFFu;
+    const uint32_t c3 = kDropout ? philox_c3(p, pk) : 0u;
+    const float nslope2 = kAlibi ? -p.alibi_slopes[bidh] * kLog2e : 0.f;   // ALiBi: exponent += -slope*log2e * |i - j|
     const uint32_t ds_row = smem_u32(sDs) + g * L::kSub + kl * 128;
 
     for (int it = 0; it < n_iter; ++it) {
@@ -546,7 +732,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
           uint32_t mine = 0;
 #pragma unroll
           for (int kg = 0; kg < 4; ++kg) {
-            const uint4 r = dropout_rand8(pk, bh, static_cast<uint32_t>(m * kBM + ql), static_cast<uint32_t>((k0 >> 3) + w * 4 + kg));
+            const uint4 r = dropout_rand8(pk, c3, bh, static_cast<uint32_t>(m * kBM + ql), static_cast<uint32_t>((k0 >> 3) + w * 4 + kg));
             const uint32_t rw[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
@@ -570,6 +756,11 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
         need_mask = true;
         const int first = kl - g * 64;     // query column c is visible iff c >= first
         colmask &= first <= 0 ? ~0ull : (first >= 64 ? 0ull : (~0ull << first));
+      }
+      if ((m + 1) * kBM > seq.seqlen_q) {  // last, partial query tile: columns beyond the sequence (their Q / dO rows may hold anything)
+        need_mask = true;
+        const int nvalid = seq.seqlen_q - m * kBM - g * 64;
+        colmask &= nvalid >= 64 ? ~0ull : (nvalid <= 0 ? 0ull : ((1ull << nvalid) - 1ull));
       }
       if (kSparse) {
         need_mask = true;
@@ -600,10 +791,18 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
 #pragma unroll
         for (int c4 = 0; c4 < 8; ++c4) {
           const float4 nl = lds128(nl_s + (ch * 32 + c4 * 4) * 4);
-          pf[ch * 32 + c4 * 4 + 0] = ex2(fmaf(pf[ch * 32 + c4 * 4 + 0], scale_log2, nl.x));
-          pf[ch * 32 + c4 * 4 + 1] = ex2(fmaf(pf[ch * 32 + c4 * 4 + 1], scale_log2, nl.y));
-          pf[ch * 32 + c4 * 4 + 2] = ex2(fmaf(pf[ch * 32 + c4 * 4 + 2], scale_log2, nl.z));
-          pf[ch * 32 + c4 * 4 + 3] = ex2(fmaf(pf[ch * 32 + c4 * 4 + 3], scale_log2, nl.w));
+          const float nlv[4] = {nl.x, nl.y, nl.z, nl.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int c = ch * 32 + c4 * 4 + e;
+            float x = fmaf(pf[c], scale_log2, nlv[e]);
+            if (kAlibi) {
+              const float rel0 = static_cast<float>(m * kBM + g * 64 - key);   // i - j at column 0 of this half
+              // causal: visible entries have i >= j, the bias is linear in the column
+              x += kCausal ? fmaf(nslope2, static_cast<float>(c), nslope2 * rel0) : nslope2 * fabsf(rel0 + static_cast<float>(c));
+            }
+            pf[c] = ex2(x);
+          }
         }
         if (need_mask) {
           const uint32_t mb = static_cast<uint32_t>(colmask >> (ch * 32));
@@ -640,6 +839,16 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
       tmem_ld32(tDP, dpr[0]);
       tmem_ld32(tDP + 32, dpr[1]);
       tmem_wait_ld();
+      if (need_mask) {
+        // masked entries: P is exactly 0 there, but dP may be anything (stray rows of a partial tile) and 0 * NaN = NaN
+#pragma unroll
+        for (int ch = 0; ch < 2; ++ch) {
+          const uint32_t mb = static_cast<uint32_t>(colmask >> (ch * 32));
+#pragma unroll
+          for (int c = 0; c < 32; ++c)
+            if (!((mb >> c) & 1u)) dpr[ch][c] = 0u;
+        }
+      }
 #pragma unroll
       for (int ch = 0; ch < 2; ++ch) {
         uint32_t dsp[16];
@@ -707,76 +916,80 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
 }
 
 // ------------------------------------------------------------------------------------------------
-// preprocess: D = rowsum(dO o O) -> softmax_d and the padded workspace copy; -lse*log2e -> workspace
-// 16 threads per query row (8 elements = 16 bytes each), 16 rows per CTA.
+// preprocess: D = rowsum(dO o O) -> softmax_d and the workspace copy; -lse*log2e -> workspace (both padded to whole
+// 128-row tiles of each sequence).  HBM-bound: 16 threads per query row (16 bytes each), 64 rows per CTA, all eight
+// loads of a thread in flight before the first use.  Rows of sequences without keys get dq = 0 here (no key-block CTA
+// will ever finalise them).
 // ------------------------------------------------------------------------------------------------
+constexpr int kPreRows = 64;
 template <bool kBf16>
-__global__ void __launch_bounds__(256) bwd_preprocess_kernel(const fa_params p, const BwdWs ws) {
+__global__ void __launch_bounds__(256) bwd_preprocess_kernel(const fa_params p, const BwdWs ws, const int n_rowblocks) {
   using T = typename Elem<kBf16>::T;
-  const int bidb = blockIdx.z, bidh = blockIdx.y;
-  const SeqInfo seq(p.cu_seqlens_q, p.cu_seqlens_k, bidb);
-  const int row = blockIdx.x * 16 + (threadIdx.x >> 4);
+  const int bidb = blockIdx.x / n_rowblocks, bidh = blockIdx.y;
+  const int rb = blockIdx.x - bidb * n_rowblocks;
+  const SeqInfo seq(p, bidb);
+  const int rows_pad = (seq.seqlen_q + kBM - 1) / kBM * kBM;       // this sequence's tile slots end here
   const int part = threadIdx.x & 15;
-  const bool valid = row < seq.seqlen_q;
-  float acc = 0.f;
-  if (valid && part * 8 < p.d) {
-    const int64_t r = seq.q_begin + row;
-    const uint4 ov = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.o) + r * p.o_row_stride + (int64_t)bidh * p.o_head_stride + part * 8));
-    const uint4 gv = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.dout) + r * p.do_row_stride + (int64_t)bidh * p.do_head_stride + part * 8));
-    const T* oe = reinterpret_cast<const T*>(&ov);
-    const T* ge = reinterpret_cast<const T*>(&gv);
+  const int row0 = rb * kPreRows + (threadIdx.x >> 4);
+  if (rb * kPreRows >= rows_pad && rb * kPreRows >= p.seqlen_q_rounded) return;
+  uint4 ov[4], gv[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int row = row0 + i * 16;
+    ov[i] = make_uint4(0u, 0u, 0u, 0u);
+    gv[i] = ov[i];
+    if (row < seq.seqlen_q && part * 8 < p.d) {
+      const int64_t r = seq.q_begin + row;
+      ov[i] = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.o) + r * p.o_row_stride + (int64_t)bidh * p.o_head_stride + part * 8));
+      gv[i] = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.dout) + r * p.do_row_stride + (int64_t)bidh * p.do_head_stride + part * 8));
+    }
+  }
+  const int64_t bh = (int64_t)bidb * p.h + bidh;
+  const int64_t stat0 = ((int64_t)bidh * ws.n_slots + tile_slot(seq.q_begin, bidb, 0)) * kBM;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int row = row0 + i * 16;
+    const bool valid = row < seq.seqlen_q;
+    const T* oe = reinterpret_cast<const T*>(&ov[i]);
+    const T* ge = reinterpret_cast<const T*>(&gv[i]);
+    float acc = 0.f;
 #pragma unroll
     for (int t = 0; t < 8; ++t) acc = fmaf(Elem<kBf16>::to_float(oe[t]), Elem<kBf16>::to_float(ge[t]), acc);
-  }
 #pragma unroll
-  for (int o = 8; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-  if (part == 0 && row < ws.sq_pad) {
-    const int64_t bh = (int64_t)bidb * p.h + bidh;
-    float nl = -INFINITY;
-    if (valid) {
-      const float lse = p.softmax_lse[bh * p.seqlen_q_rounded + row];
-      if (lse != -INFINITY) nl = -lse * kLog2e;
+    for (int o = 8; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (valid && seq.seqlen_k <= 0 && part * 8 < p.d)
+      *reinterpret_cast<uint4*>(reinterpret_cast<T*>(p.dq) + (int64_t)(seq.q_begin + row) * p.dq_row_stride + (int64_t)bidh * p.dq_head_stride + part * 8) =
+          make_uint4(0u, 0u, 0u, 0u);
+    if (part == 0) {
+      if (row < rows_pad) {
+        float nl = -INFINITY;
+        if (valid) {
+          const float lse = p.softmax_lse[bh * p.seqlen_q_rounded + row];
+          if (lse != -INFINITY) nl = -lse * kLog2e;
+        }
+        ws.nl[stat0 + row] = nl;
+        ws.dsum[stat0 + row] = valid ? acc : 0.f;
+      }
+      if (row < p.seqlen_q_rounded) p.softmax_d[bh * p.seqlen_q_rounded + row] = valid ? acc : 0.f;
     }
-    ws.nl[bh * ws.sq_pad + row] = nl;
-    ws.dsum[bh * ws.sq_pad + row] = valid ? acc : 0.f;
-    if (row < p.seqlen_q_rounded) p.softmax_d[bh * p.seqlen_q_rounded + row] = valid ? acc : 0.f;
   }
 }
 
 // ------------------------------------------------------------------------------------------------
-// postprocess: dq = scale * dq_accum (tile layout [4 row quarters][DPAD/4][32 rows][4]) -> 16 bit, caller's strides
+// postprocess (blocksparse variant only): dq = scale * dq_accum -> 16 bit, caller's strides; zeros written back
 // ------------------------------------------------------------------------------------------------
 template <bool kBf16, int DPAD>
-__global__ void __launch_bounds__(256) bwd_postprocess_kernel(const fa_params p, const BwdWs ws) {
-  using T = typename Elem<kBf16>::T;
-  const int bidb = blockIdx.z, bidh = blockIdx.y, m = blockIdx.x;
-  const SeqInfo seq(p.cu_seqlens_q, p.cu_seqlens_k, bidb);
-  const int r = threadIdx.x & 127, half = threadIdx.x >> 7;
-  const int row = m * kBM + r;
-  if (row >= seq.seqlen_q) return;
-  const float* tile = ws.dq_accum + (((int64_t)bidb * p.h + bidh) * ws.n_qtiles + m) * (kBM * DPAD);
-  T* out = reinterpret_cast<T*>(p.dq) + (int64_t)(seq.q_begin + row) * p.dq_row_stride + (int64_t)bidh * p.dq_head_stride;
-  const float sc = p.softmax_scale;
-#pragma unroll
-  for (int cg = 0; cg < DPAD / 32; ++cg) {          // 16 columns per step
-    const int col = half * (DPAD / 2) + cg * 16;
-    if (col >= p.d) break;
-    float4 v[4];
-#pragma unroll
-    for (int gq = 0; gq < 4; ++gq)
-      v[gq] = *reinterpret_cast<const float4*>(tile + (r >> 5) * (32 * DPAD) + (col / 4 + gq) * 128 + (r & 31) * 4);
-    uint4 a, b;
-    a.x = pack2<kBf16>(v[0].x * sc, v[0].y * sc);
-    a.y = pack2<kBf16>(v[0].z * sc, v[0].w * sc);
-    a.z = pack2<kBf16>(v[1].x * sc, v[1].y * sc);
-    a.w = pack2<kBf16>(v[1].z * sc, v[1].w * sc);
-    b.x = pack2<kBf16>(v[2].x * sc, v[2].y * sc);
-    b.y = pack2<kBf16>(v[2].z * sc, v[2].w * sc);
-    b.z = pack2<kBf16>(v[3].x * sc, v[3].y * sc);
-    b.w = pack2<kBf16>(v[3].z * sc, v[3].w * sc);
-    *reinterpret_cast<uint4*>(out + col) = a;
-    if (col + 8 < p.d) *reinterpret_cast<uint4*>(out + col + 8) = b;
-  }
+__global__ void __launch_bounds__(128) bwd_postprocess_kernel(const fa_params p, const BwdWs ws, const int n_qtiles) {
+  const int bidb = blockIdx.x / n_qtiles, bidh = blockIdx.y;
+  const int m = blockIdx.x - bidb * n_qtiles;
+  const SeqInfo seq(p, bidb);
+  if (m * kBM >= seq.seqlen_q) return;
+  const int q4 = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = m * kBM + q4 * 32 + lane;
+  float* acc = ws.dq_accum + ((int64_t)bidh * ws.n_slots + tile_slot(seq.q_begin, bidb, m)) * (kBM * DPAD) + q4 * (32 * DPAD);
+  uint16_t* out = row < seq.seqlen_q ? reinterpret_cast<uint16_t*>(p.dq) + (int64_t)(seq.q_begin + row) * p.dq_row_stride + (int64_t)bidh * p.dq_head_stride
+                                     : nullptr;
+  finalize_dq_quarter<DPAD, kBf16, 4>(acc, out, p.d, p.softmax_scale, lane);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -785,38 +998,40 @@ __global__ void __launch_bounds__(256) bwd_postprocess_kernel(const fa_params p,
 inline uint64_t align256(uint64_t x) { return (x + 255) & ~uint64_t(255); }
 
 struct BwdWsLayout {
-  uint64_t nl_off, dsum_off, accum_off, total;
-  int sq_pad, n_qtiles, dpad;
+  uint64_t nl_off, dsum_off, accum_off, count_off, total;
+  int n_slots, dpad;
 };
 
 BwdWsLayout bwd_ws_layout(const fa_params& p) {
   BwdWsLayout l;
-  l.n_qtiles = (p.max_seqlen_q + kBM - 1) / kBM;
-  l.sq_pad = l.n_qtiles * kBM;
+  l.n_slots = (p.total_q >> 7) + p.b + 1;
   l.dpad = p.d <= 64 ? 64 : 128;
-  const uint64_t rows = (uint64_t)p.b * p.h * l.sq_pad;
-  l.nl_off = 0;
-  l.dsum_off = align256(rows * 4);
-  l.accum_off = l.dsum_off + align256(rows * 4);
-  l.total = l.accum_off + align256(rows * l.dpad * 4);
+  const uint64_t rows = (uint64_t)p.h * l.n_slots * kBM;
+  l.accum_off = 0;                                         // [0, nl_off): the "zero on entry / zero on exit" region
+  l.count_off = align256(rows * l.dpad * 4);
+  l.nl_off = l.count_off + align256((uint64_t)p.h * l.n_slots * 4 * 4);
+  l.dsum_off = l.nl_off + align256(rows * 4);
+  l.total = l.dsum_off + align256(rows * 4);
   return l;
 }
 
-template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse>
+template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse, bool kAlibi>
 cudaError_t launch_bwd_variant(const BwdTensorMaps& maps, const fa_params& p, const BlockMaskView& bm, const BwdWs& ws,
                                cudaStream_t stream) {
-  auto kernel = bwd_sm100_kernel<DPAD, kBf16, kCausal, kDropout, kSparse>;
+  auto kernel = bwd_sm100_kernel<DPAD, kBf16, kCausal, kDropout, kSparse, kAlibi>;
   constexpr int smem = BwdSmem<DPAD>::kDynamicBytes;
-  static bool configured[16] = {};   // per device (as in the forward): the attribute call costs ~1.5 us of host time
+  static std::atomic<uint64_t> configured{0};   // bit per device (as in the forward)
   int dev = 0;
   cudaGetDevice(&dev);
-  if (dev >= 16 || !configured[dev]) {
+  if (dev >= 64 || !((configured.load(std::memory_order_acquire) >> dev) & 1u)) {
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
-    if (dev < 16) configured[dev] = true;
+    if (dev < 64) configured.fetch_or(uint64_t(1) << dev, std::memory_order_release);
   }
   const int n_kblocks = (p.max_seqlen_k + kBN - 1) / kBN;
-  const dim3 grid = kCausal ? dim3(n_kblocks * p.h * p.b, 1, 1) : dim3(n_kblocks, p.h, p.b);
+  const int64_t n_ctas = (int64_t)n_kblocks * p.h * p.b;
+  if (n_ctas > 0x7fffffffLL) return cudaErrorInvalidConfiguration;
+  const dim3 grid(static_cast<unsigned>(n_ctas), 1, 1);
   const int bh_group = causal_bh_group(p.max_seqlen_q > p.max_seqlen_k ? p.max_seqlen_q : p.max_seqlen_k);
   void* span = timing_begin(stream);
   kernel<<<grid, kBwdThreads, smem, stream>>>(maps, p, bm, ws, n_kblocks, bh_group, make_philox_key(p.philox_seed, p.philox_offset));
@@ -830,20 +1045,26 @@ cudaError_t dispatch_bwd_flags(const BwdTensorMaps& maps, const fa_params& p, co
                                cudaStream_t stream) {
   const bool drop = p.p_dropout > 0.f;
   if (bm.dense != nullptr) {
-    return drop ? launch_bwd_variant<DPAD, kBf16, false, true, true>(maps, p, bm, ws, stream)
-                : launch_bwd_variant<DPAD, kBf16, false, false, true>(maps, p, bm, ws, stream);
+    return drop ? launch_bwd_variant<DPAD, kBf16, false, true, true, false>(maps, p, bm, ws, stream)
+                : launch_bwd_variant<DPAD, kBf16, false, false, true, false>(maps, p, bm, ws, stream);
   }
-  if (p.is_causal) {
-    return drop ? launch_bwd_variant<DPAD, kBf16, true, true, false>(maps, p, bm, ws, stream)
-                : launch_bwd_variant<DPAD, kBf16, true, false, false>(maps, p, bm, ws, stream);
+  const int sel = (p.is_causal ? 4 : 0) | (drop ? 2 : 0) | (p.alibi_slopes != nullptr ? 1 : 0);
+  switch (sel) {
+    case 0: return launch_bwd_variant<DPAD, kBf16, false, false, false, false>(maps, p, bm, ws, stream);
+    case 1: return launch_bwd_variant<DPAD, kBf16, false, false, false, true>(maps, p, bm, ws, stream);
+    case 2: return launch_bwd_variant<DPAD, kBf16, false, true, false, false>(maps, p, bm, ws, stream);
+    case 3: return launch_bwd_variant<DPAD, kBf16, false, true, false, true>(maps, p, bm, ws, stream);
+    case 4: return launch_bwd_variant<DPAD, kBf16, true, false, false, false>(maps, p, bm, ws, stream);
+    case 5: return launch_bwd_variant<DPAD, kBf16, true, false, false, true>(maps, p, bm, ws, stream);
+    case 6: return launch_bwd_variant<DPAD, kBf16, true, true, false, false>(maps, p, bm, ws, stream);
+    default: return launch_bwd_variant<DPAD, kBf16, true, true, false, true>(maps, p, bm, ws, stream);
   }
-  return drop ? launch_bwd_variant<DPAD, kBf16, false, true, false>(maps, p, bm, ws, stream)
-              : launch_bwd_variant<DPAD, kBf16, false, false, false>(maps, p, bm, ws, stream);
 }
 
 }  // namespace
 
 uint64_t bwd_sm100_workspace_bytes(const fa_params& p) { return bwd_ws_layout(p).total; }
+uint64_t bwd_sm100_workspace_zero_bytes(const fa_params& p) { return bwd_ws_layout(p).nl_off; }
 
 #ifdef FA_BWD_TRACE
 extern "C" __attribute__((visibility("default"))) int fa_debug_read_bwd_trace(long long* host, int n) {
@@ -858,8 +1079,13 @@ cudaError_t launch_bwd_sm100(const fa_params& p, const BlockMaskView& bm, void* 
                              const char** err_msg) {
   *err_msg = nullptr;
   const BwdWsLayout l = bwd_ws_layout(p);
-  if (bm.dense != nullptr && l.n_qtiles > kMaxSparseTiles) {
+  const int n_qtiles = (p.max_seqlen_q + kBM - 1) / kBM;
+  if (bm.dense != nullptr && n_qtiles > kMaxSparseTiles) {
     *err_msg = "blocksparse backward supports at most 65536 queries per sequence";
+    return cudaErrorInvalidValue;
+  }
+  if ((int64_t)n_qtiles * p.b > 0x7fffffffLL || p.h > 65535) {
+    *err_msg = "backward grid too large (batch x query tiles must fit 31 bits, heads 16 bits)";
     return cudaErrorInvalidValue;
   }
   uint8_t* base = static_cast<uint8_t*>(workspace);
@@ -867,15 +1093,19 @@ cudaError_t launch_bwd_sm100(const fa_params& p, const BlockMaskView& bm, void* 
   ws.nl = reinterpret_cast<float*>(base + l.nl_off);
   ws.dsum = reinterpret_cast<float*>(base + l.dsum_off);
   ws.dq_accum = reinterpret_cast<float*>(base + l.accum_off);
-  ws.sq_pad = l.sq_pad;
-  ws.n_qtiles = l.n_qtiles;
+  ws.dq_count = reinterpret_cast<uint32_t*>(base + l.count_off);
+  ws.n_slots = l.n_slots;
   cudaError_t e;
-  if (l.n_qtiles > 0) {
-    e = cudaMemsetAsync(ws.dq_accum, 0, (uint64_t)p.b * p.h * l.sq_pad * l.dpad * 4, stream);
+  if (!(p.flags & FA_FLAG_WS_ZEROED)) {
+    e = cudaMemsetAsync(base + l.accum_off, 0, l.nl_off - l.accum_off, stream);
     if (e != cudaSuccess) return e;
-    const dim3 grid(l.sq_pad / 16, p.h, p.b);
-    if (p.is_bf16) bwd_preprocess_kernel<true><<<grid, 256, 0, stream>>>(p, ws);
-    else bwd_preprocess_kernel<false><<<grid, 256, 0, stream>>>(p, ws);
+  }
+  if (n_qtiles > 0 && p.total_q > 0) {
+    const int rows_max = max(n_qtiles * kBM, p.seqlen_q_rounded);
+    const int n_rowblocks = (rows_max + kPreRows - 1) / kPreRows;
+    const dim3 grid(static_cast<unsigned>(n_rowblocks * p.b), p.h, 1);
+    if (p.is_bf16) bwd_preprocess_kernel<true><<<grid, 256, 0, stream>>>(p, ws, n_rowblocks);
+    else bwd_preprocess_kernel<false><<<grid, 256, 0, stream>>>(p, ws, n_rowblocks);
     count_launch();
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
@@ -896,14 +1126,14 @@ cudaError_t launch_bwd_sm100(const fa_params& p, const BlockMaskView& bm, void* 
     else e = p.is_bf16 ? dispatch_bwd_flags<128, true>(maps, p, bm, ws, stream) : dispatch_bwd_flags<128, false>(maps, p, bm, ws, stream);
     if (e != cudaSuccess) return e;
   }
-  if (l.n_qtiles > 0 && p.total_q > 0) {
-    const dim3 grid(l.n_qtiles, p.h, p.b);
+  if (bm.dense != nullptr && n_qtiles > 0 && p.total_q > 0) {
+    const dim3 grid(static_cast<unsigned>(n_qtiles * p.b), p.h, 1);
     if (l.dpad == 64) {
-      if (p.is_bf16) bwd_postprocess_kernel<true, 64><<<grid, 256, 0, stream>>>(p, ws);
-      else bwd_postprocess_kernel<false, 64><<<grid, 256, 0, stream>>>(p, ws);
+      if (p.is_bf16) bwd_postprocess_kernel<true, 64><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
+      else bwd_postprocess_kernel<false, 64><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
     } else {
-      if (p.is_bf16) bwd_postprocess_kernel<true, 128><<<grid, 256, 0, stream>>>(p, ws);
-      else bwd_postprocess_kernel<false, 128><<<grid, 256, 0, stream>>>(p, ws);
+      if (p.is_bf16) bwd_postprocess_kernel<true, 128><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
+      else bwd_postprocess_kernel<false, 128><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
     }
     count_launch();
     e = cudaGetLastError();

@@ -56,8 +56,8 @@ FA_HD uint4 philox4x32_7(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, con
 }
 
 // 8 uniforms (16 bit each) for keys 8*kgroup .. 8*kgroup+7 of query row qrow.
-FA_HD uint4 dropout_rand8(const PhiloxKey& key, uint32_t bh, uint32_t qrow, uint32_t kgroup) {
-  return philox4x32_7(qrow, kgroup, bh, key.c3, key);
+FA_HD uint4 dropout_rand8(const PhiloxKey& key, uint32_t c3, uint32_t bh, uint32_t qrow, uint32_t kgroup) {
+  return philox4x32_7(qrow, kgroup, bh, c3, key);
 }
 FA_HD uint32_t rand8_get(const uint4& r, int e) {   // e in [0, 8)
   const uint32_t w = (e >> 1) == 0 ? r.x : (e >> 1) == 1 ? r.y : (e >> 1) == 2 ? r.z : r.w;
@@ -73,13 +73,20 @@ FA_HD uint32_t keep_threshold_u16(float p_dropout) {
 // ------------------------------------------------------------------------------------------------
 struct SeqInfo {
   int q_begin, k_begin, seqlen_q, seqlen_k;
-  __device__ __forceinline__ SeqInfo(const int32_t* cu_q, const int32_t* cu_k, int b) {
-    q_begin = cu_q[b];
-    k_begin = cu_k[b];
-    seqlen_q = cu_q[b + 1] - q_begin;
-    seqlen_k = cu_k[b + 1] - k_begin;
+  // seqused_* (optional): the sequence uses only that many rows from its begin; cu_seqlens[b + 1] is then not read
+  __device__ __forceinline__ SeqInfo(const fa_params& p, int b) {
+    q_begin = p.cu_seqlens_q[b];
+    k_begin = p.cu_seqlens_k[b];
+    seqlen_q = p.seqused_q != nullptr ? p.seqused_q[b] : p.cu_seqlens_q[b + 1] - q_begin;
+    seqlen_k = p.seqused_k != nullptr ? p.seqused_k[b] : p.cu_seqlens_k[b + 1] - k_begin;
   }
 };
+
+// Low word of the Philox offset a kernel uses: the host value plus the optional device-side counter
+// (fa_params.philox_offset_ptr -- graph-capturable dropout).  Only counter word c3 depends on it.
+__device__ __forceinline__ uint32_t philox_c3(const fa_params& p, const PhiloxKey& pk) {
+  return p.philox_offset_ptr != nullptr ? pk.c3 + static_cast<uint32_t>(*p.philox_offset_ptr) : pk.c3;
+}
 
 template <bool kBf16>
 struct Elem;
@@ -121,8 +128,7 @@ __device__ __forceinline__ CtaCoord decode_cta(int lin, int nx, int n_bh, int bh
 // 2048 -- i.e. roughly 64 MB of Q + dO + fp32 dQ accumulator in the backward, half the L2.  Larger groups thrash the L2
 // (-20 % at one group for the whole batch), much smaller ones lengthen the tail.  FA_BH_GROUP overrides it (experiments).
 inline int causal_bh_group(int max_seqlen) {
-  const char* e = getenv("FA_BH_GROUP");
-  const int forced = e != nullptr ? atoi(e) : 0;
+  static const int forced = [] { const char* e = getenv("FA_BH_GROUP"); return e != nullptr ? atoi(e) : 0; }();   // read once
   if (forced > 0) return forced;
   const int g = 65536 / (max_seqlen > 0 ? max_seqlen : 1);
   return g < 1 ? 1 : (g > kBhGroupMax ? kBhGroupMax : g);

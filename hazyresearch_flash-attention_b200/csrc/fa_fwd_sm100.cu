@@ -10,6 +10,8 @@
 // TMEM columns: S0 [0,128) | S1 [128,256) | O0 [256,256+DPAD) | O1 [384,384+DPAD).
 #include <cudaTypedefs.h>
 
+#include <atomic>
+
 #include "fa_common.cuh"
 #include "fa_kernels.h"
 #include "sm100_ptx.cuh"
@@ -39,8 +41,8 @@ struct FwdSmem {
   static constexpr int kKOff = kQOff + kTilesPerCta * kTileBytes;
   static constexpr int kVOff = kKOff + kStages * kTileBytes;
   static constexpr int kBarOff = kVOff + kStages * kTileBytes;
-  // barriers: q_full[2], s_full[2], o_full[2], p_full[2][kPChunks], k_full[S], k_empty[S], v_full[S], v_empty[S]
-  static constexpr int kNumBars = 6 + 2 * kPChunks + 4 * kStages;
+  // barriers: q_full[2], s_full[2], o_full[2], p_full[2][kPChunks], k_full[S], k_empty[S], v_full[S], v_empty[S], v_fix
+  static constexpr int kNumBars = 7 + 2 * kPChunks + 4 * kStages;
   static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
   static constexpr int kListOff = kTmemPtrOff + 16;              // blocksparse: active KV block list (int16)
   static constexpr int kMaxListEntries = 1024;
@@ -70,7 +72,7 @@ __device__ long long g_fwd_cta[8192 * 8];   // per CTA: smid, globaltimer start,
 #define FA_FCTA(slot, val) do { } while (0)
 #endif
 
-template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse>
+template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse, bool kAlibi>
 __global__ void __launch_bounds__(kNumThreads, 1)
 fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, const BlockMaskView bm, const int n_mblocks,
                  const int bh_group, const int pingpong, const PhiloxKey pk) {   // round keys precomputed on the host: they are read straight from the constant bank
@@ -80,7 +82,8 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // causal: 1-D launch, heaviest (latest) query blocks first within groups of (batch, head) pairs; else grid (block, h, b)
+  // 1-D launch (no 65535 limit on batch or heads).  causal: heaviest (latest) query blocks first within groups of
+  // (batch, head) pairs; else block-major inside each (batch, head) pair
   int bidb, bidh, m_block;
   if (kCausal) {
     const CtaCoord c = decode_cta(blockIdx.x, n_mblocks, p.b * p.h, bh_group);
@@ -88,9 +91,12 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
     bidb = c.bh / p.h;
     bidh = c.bh - bidb * p.h;
   } else {
-    bidb = blockIdx.z, bidh = blockIdx.y, m_block = blockIdx.x;
+    const int pair = blockIdx.x / n_mblocks;
+    m_block = blockIdx.x - pair * n_mblocks;
+    bidb = pair / p.h;
+    bidh = pair - bidb * p.h;
   }
-  const SeqInfo seq(p.cu_seqlens_q, p.cu_seqlens_k, bidb);
+  const SeqInfo seq(p, bidb);
   const int q0 = m_block * (kBlockM * kTilesPerCta);
   if (q0 >= seq.seqlen_q) return;   // CTA-uniform
 #ifdef FA_BWD_TRACE
@@ -113,6 +119,7 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
   uint64_t* k_empty = k_full + ST;
   uint64_t* v_full = k_empty + ST;
   uint64_t* v_empty = v_full + ST;
+  uint64_t* v_fix = v_empty + ST;
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + L::kTmemPtrOff);
   int16_t* blk_list = reinterpret_cast<int16_t*>(smem + L::kListOff);
   __shared__ int s_num_active;
@@ -160,6 +167,15 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
     for (int t = 0; t < kTilesPerCta; ++t) cnt[t] = cnt[t] > 0 ? nu : 0;
   }
 
+  // Isolation of sequences (the reference predicates its loads on row < seqlen and zero-fills): the last key block may
+  // reach past the sequence, and its V rows then hold the next sequence's tokens or whatever lies behind the packed
+  // batch.  P is exactly 0 there, but 0 * NaN in O += P V would poison valid rows -- so the V tile of such a block lands
+  // on its own barrier (v_fix), warp 10 zeroes the rows beyond the sequence and only then completes v_full for the MMA
+  // warp.  (Stray K rows only produce S columns that the mask overwrites with -inf; stray Q rows are never stored.)
+  const int j_last = nu > 0 ? (kSparse ? static_cast<int>(blk_list[nu - 1]) : nu - 1) : 0;
+  const int v_valid_last = seq.seqlen_k - j_last * kBlockN;
+  const bool v_partial = nu > 0 && v_valid_last < kBlockN;
+
   uint8_t* sQ = smem + L::kQOff;
   uint8_t* sK = smem + L::kKOff;
   uint8_t* sV = smem + L::kVOff;
@@ -177,6 +193,7 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
     // the loads run under the TMEM allocation and the CTA-wide barrier below instead of after them.
     mbar_init(&q_full[0], 1);
     mbar_init(&q_full[1], 1);
+    mbar_init(v_fix, 1);
     for (int s = 0; s < ST; ++s) {
       mbar_init(&k_full[s], 1);
       mbar_init(&k_empty[s], 1);
@@ -203,10 +220,11 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
 #pragma unroll
       for (int c = 0; c < DPAD / 64; ++c)
         tma_load_3d(sK + c * L::kSubTileBytes, &maps.k, &k_full[0], c * 64, bidh, seq.k_begin + j0 * kBlockN);
-      mbar_arrive_expect_tx(&v_full[0], L::kTileBytes);
+      uint64_t* vbar = (nu == 1 && v_partial) ? v_fix : &v_full[0];
+      mbar_arrive_expect_tx(vbar, L::kTileBytes);
 #pragma unroll
       for (int c = 0; c < DPAD / 64; ++c)
-        tma_load_3d(sV + c * L::kSubTileBytes, &maps.v, &v_full[0], c * 64, bidh, seq.k_begin + j0 * kBlockN);
+        tma_load_3d(sV + c * L::kSubTileBytes, &maps.v, vbar, c * 64, bidh, seq.k_begin + j0 * kBlockN);
     }
   }
   __syncwarp();
@@ -237,12 +255,28 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
             tma_load_3d(sK + s * L::kTileBytes + c * L::kSubTileBytes, &maps.k, &k_full[s], c * 64, bidh,
                         seq.k_begin + j * kBlockN);
           mbar_wait(&v_empty[s], ph ^ 1);
-          mbar_arrive_expect_tx(&v_full[s], L::kTileBytes);
+          uint64_t* vbar = (u + 1 == nu && v_partial) ? v_fix : &v_full[s];
+          mbar_arrive_expect_tx(vbar, L::kTileBytes);
 #pragma unroll
           for (int c = 0; c < DPAD / 64; ++c)
-            tma_load_3d(sV + s * L::kTileBytes + c * L::kSubTileBytes, &maps.v, &v_full[s], c * 64, bidh,
+            tma_load_3d(sV + s * L::kTileBytes + c * L::kSubTileBytes, &maps.v, vbar, c * 64, bidh,
                         seq.k_begin + j * kBlockN);
         }
+      }
+    } else if (warp == 10) {
+      // ===================================== V tail zero-fill ==================================
+      if (v_partial) {
+        const int s = (nu - 1) % ST;
+        mbar_wait(v_fix, 0);
+        const int nrows = kBlockN - v_valid_last;   // v_valid_last >= 1: the block exists
+        const uint32_t base = smem_u32(sV) + s * L::kTileBytes + v_valid_last * 128;
+        for (int idx = lane; idx < nrows * 8 * (DPAD / 64); idx += 32) {
+          const int sub = idx / (nrows * 8), r = idx - sub * (nrows * 8);   // 128-byte rows; the swizzle stays inside a row
+          asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};\n" ::"r"(base + sub * L::kSubTileBytes + r * 16), "r"(0u) : "memory");
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&v_full[s]);
       }
     } else if (warp == 9) {
       // ===================================== MMA issuer =======================================
@@ -337,6 +371,12 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
     const uint32_t bh = bidb * p.h + bidh;
     const uint32_t keep_thr = keep_threshold_u16(p.p_dropout);
     const uint32_t keep_thr_hi = (keep_thr << 16) | 0xFFFFu;
+    const uint32_t c3 = kDropout ? philox_c3(p, pk) : 0u;
+    // ALiBi (kAlibi): the scores are moved to the scaled log2 domain with the bias added right after the TMEM load,
+    //     x = s * scale*log2e - slope*log2e * |i - j|,
+    // and everything downstream works on x with a unit scale.
+    const float sl2 = kAlibi ? 1.f : scale_log2;
+    const float slope2 = kAlibi ? p.alibi_slopes[bidh] * kLog2e : 0.f;
 
     float m = -INFINITY, l = 0.f;
     const int my_cnt = cnt[t];
@@ -361,6 +401,17 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
         tmem_wait_ld();
       }
       if ((warp & 3) == 0) FA_FTRACE(u, 8 * t + 1);
+      if (kAlibi) {
+        const float rel0 = static_cast<float>(qi - j * kBlockN);   // i - j at column 0
+        if (kCausal) {   // visible entries have i >= j: the bias is linear in the column
+          const float b0 = -slope2 * rel0;
+#pragma unroll
+          for (int c = 0; c < kBlockN; ++c) sv[c] = fmaf(sv[c], scale_log2, fmaf(slope2, static_cast<float>(c), b0));
+        } else {
+#pragma unroll
+          for (int c = 0; c < kBlockN; ++c) sv[c] = fmaf(sv[c], scale_log2, -slope2 * fabsf(rel0 - static_cast<float>(c)));
+        }
+      }
       // ---- masking: key padding, causal (top-left aligned: key <= query), blocksparse ----
       int limit = seq.seqlen_k - j * kBlockN;
       if (kCausal) limit = min(limit, qi + 1 - j * kBlockN);
@@ -384,11 +435,11 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
       if (u == 0) {
         m = m_blk;
       } else {
-        const bool need = (m_blk - m) * scale_log2 > kRescaleThreshold;   // false on NaN (-inf - -inf)
+        const bool need = (m_blk - m) * sl2 > kRescaleThreshold;   // false on NaN (-inf - -inf)
         if (__any_sync(0xffffffffu, need)) {
           const float m_new = fmaxf(m, m_blk);
           const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-          const float alpha = ex2((m - m_use) * scale_log2);
+          const float alpha = ex2((m - m_use) * sl2);
           l *= alpha;
           m = m_new;
 #pragma unroll
@@ -405,7 +456,7 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
       // ---- exponentials, row sum, dropout, pack to 16 bit: one 32-key chunk at a time, each handed over as soon as its
       //      tcgen05.st has landed (the wait for chunk c is taken after the arithmetic of chunk c+1) ----
       const float m_use = (m == -INFINITY) ? 0.f : m;
-      const float neg_ms = -m_use * scale_log2;
+      const float neg_ms = -m_use * sl2;
       if ((warp & 3) == 0) FA_FTRACE(u, 8 * t + 2);
       if (u < n_turns) named_bar_sync(2 + t, 256);            // wait for this tile's turn on the MUFU
       if ((warp & 3) == 0) FA_FTRACE(u, 8 * t + 3);
@@ -415,8 +466,8 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
       for (int ch = 0; ch < kPChunks; ++ch) {
 #pragma unroll
         for (int c = ch * kCw; c < (ch + 1) * kCw; c += 4) {
-          ffma2(sv[c], sv[c + 1], scale_log2, neg_ms);          // packed pairs: half the issue slots of FFMA / FADD
-          ffma2(sv[c + 2], sv[c + 3], scale_log2, neg_ms);
+          ffma2(sv[c], sv[c + 1], sl2, neg_ms);          // packed pairs: half the issue slots of FFMA / FADD
+          ffma2(sv[c + 2], sv[c + 3], sl2, neg_ms);
           sv[c] = ex2(sv[c]);
           sv[c + 1] = ex2(sv[c + 1]);
           sv[c + 2] = ex2(sv[c + 2]);
@@ -427,7 +478,7 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
         if (kDropout) {
 #pragma unroll
           for (int g = ch * (kCw / 8); g < (ch + 1) * (kCw / 8); ++g) {
-            const uint4 r = dropout_rand8(pk, bh, static_cast<uint32_t>(qi), static_cast<uint32_t>(j * (kBlockN / 8) + g));
+            const uint4 r = dropout_rand8(pk, c3, bh, static_cast<uint32_t>(qi), static_cast<uint32_t>(j * (kBlockN / 8) + g));
             const uint32_t w[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
@@ -461,7 +512,7 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
       const bool dead = (l == 0.f) || (l != l);
       const float inv_l = dead ? 1.f : 1.f / l;
       const float out_scale = inv_l * (kDropout ? 1.f / (1.f - p.p_dropout) : 1.f);
-      const float lse = dead ? -INFINITY : (m * scale_log2 + log2f(l)) * kLn2;
+      const float lse = dead ? -INFINITY : (m * sl2 + log2f(l)) * kLn2;
       if (my_cnt > 0) {
         mbar_wait(&o_full[t], 0);
         tc_fence_after();
@@ -536,29 +587,28 @@ bool make_tensor_map_3d(CUtensorMap* map, const void* base, int d, int h, int64_
 
 namespace {
 
-template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse>
+template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse, bool kAlibi>
 cudaError_t launch_fwd_variant(const FwdTensorMaps& maps, const fa_params& p, const BlockMaskView& bm, cudaStream_t stream) {
-  auto kernel = fwd_sm100_kernel<DPAD, kBf16, kCausal, kDropout, kSparse>;
+  auto kernel = fwd_sm100_kernel<DPAD, kBf16, kCausal, kDropout, kSparse, kAlibi>;
   constexpr int smem = FwdSmem<DPAD>::kDynamicBytes;
-  static bool configured[16] = {};   // per device
+  static std::atomic<uint64_t> configured{0};   // bit per device: the attribute call costs ~1.5 us of host time
   int dev = 0;
   cudaGetDevice(&dev);
-  if (dev < 16 && !configured[dev]) {
+  if (dev >= 64 || !((configured.load(std::memory_order_acquire) >> dev) & 1u)) {
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
-    configured[dev] = true;
-  } else if (dev >= 16) {
-    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return e;
+    if (dev < 64) configured.fetch_or(uint64_t(1) << dev, std::memory_order_release);
   }
   const int n_mblocks = (p.max_seqlen_q + kBlockM * kTilesPerCta - 1) / (kBlockM * kTilesPerCta);
-  const dim3 grid = kCausal ? dim3(n_mblocks * p.h * p.b, 1, 1) : dim3(n_mblocks, p.h, p.b);
+  const int64_t n_ctas = (int64_t)n_mblocks * p.h * p.b;
+  if (n_ctas > 0x7fffffffLL) return cudaErrorInvalidConfiguration;
+  const dim3 grid(static_cast<unsigned>(n_ctas), 1, 1);
   const int bh_group = causal_bh_group(p.max_seqlen_q > p.max_seqlen_k ? p.max_seqlen_q : p.max_seqlen_k);
   // exponential-phase ping-pong (see the kernel).  Measured (profiles/r01_kernel_experiments_ab.log, after the FFMA2 change):
   // +7-10 % at d = 64 (+1-7 % with dropout); at d = 128 neutral (causal) to -3 % (non-causal): there the second tile fills
   // the MUFU bubbles the first one leaves around its TMEM stores better than the turn token does.  So: d <= 64 only.
-  const char* pp_env = getenv("FA_FWD_PINGPONG");
-  const int pingpong = pp_env != nullptr ? atoi(pp_env) : (DPAD == 64 ? 1 : 0);
+  static const int pp_forced = [] { const char* e = getenv("FA_FWD_PINGPONG"); return e != nullptr ? atoi(e) : -1; }();   // experiments; read once
+  const int pingpong = pp_forced >= 0 ? pp_forced : (DPAD == 64 ? 1 : 0);
   void* span = timing_begin(stream);
   kernel<<<grid, kNumThreads, smem, stream>>>(maps, p, bm, n_mblocks, bh_group, pingpong, make_philox_key(p.philox_seed, p.philox_offset));
   timing_end(span, 0, stream);
@@ -570,15 +620,20 @@ template <int DPAD, bool kBf16>
 cudaError_t dispatch_flags(const FwdTensorMaps& maps, const fa_params& p, const BlockMaskView& bm, cudaStream_t stream) {
   const bool drop = p.p_dropout > 0.f;
   if (bm.dense != nullptr) {
-    return drop ? launch_fwd_variant<DPAD, kBf16, false, true, true>(maps, p, bm, stream)
-                : launch_fwd_variant<DPAD, kBf16, false, false, true>(maps, p, bm, stream);
+    return drop ? launch_fwd_variant<DPAD, kBf16, false, true, true, false>(maps, p, bm, stream)
+                : launch_fwd_variant<DPAD, kBf16, false, false, true, false>(maps, p, bm, stream);
   }
-  if (p.is_causal) {
-    return drop ? launch_fwd_variant<DPAD, kBf16, true, true, false>(maps, p, bm, stream)
-                : launch_fwd_variant<DPAD, kBf16, true, false, false>(maps, p, bm, stream);
+  const int sel = (p.is_causal ? 4 : 0) | (drop ? 2 : 0) | (p.alibi_slopes != nullptr ? 1 : 0);
+  switch (sel) {
+    case 0: return launch_fwd_variant<DPAD, kBf16, false, false, false, false>(maps, p, bm, stream);
+    case 1: return launch_fwd_variant<DPAD, kBf16, false, false, false, true>(maps, p, bm, stream);
+    case 2: return launch_fwd_variant<DPAD, kBf16, false, true, false, false>(maps, p, bm, stream);
+    case 3: return launch_fwd_variant<DPAD, kBf16, false, true, false, true>(maps, p, bm, stream);
+    case 4: return launch_fwd_variant<DPAD, kBf16, true, false, false, false>(maps, p, bm, stream);
+    case 5: return launch_fwd_variant<DPAD, kBf16, true, false, false, true>(maps, p, bm, stream);
+    case 6: return launch_fwd_variant<DPAD, kBf16, true, true, false, false>(maps, p, bm, stream);
+    default: return launch_fwd_variant<DPAD, kBf16, true, true, false, true>(maps, p, bm, stream);
   }
-  return drop ? launch_fwd_variant<DPAD, kBf16, false, true, false>(maps, p, bm, stream)
-              : launch_fwd_variant<DPAD, kBf16, false, false, false>(maps, p, bm, stream);
 }
 
 }  // namespace

@@ -29,6 +29,7 @@ cudaError_t launch_bwd_sm100(const fa_params& p, const BlockMaskView& bm, void* 
 bool make_tensor_map_3d(CUtensorMap* map, const void* base, int d, int h, int64_t total, int64_t row_stride,
                         int64_t head_stride, int box_rows);
 uint64_t bwd_sm100_workspace_bytes(const fa_params& p);
+uint64_t bwd_sm100_workspace_zero_bytes(const fa_params& p);   // the scratch starts with this many zero-on-entry / zero-on-exit bytes
 
 // --- small utility kernels (fa_api.cu) ---
 cudaError_t launch_expand_blockmask(const int32_t* converted, int nrow, int ncol, uint8_t* dense, cudaStream_t stream);

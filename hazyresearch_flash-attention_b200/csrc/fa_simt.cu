@@ -74,12 +74,14 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) simt_fwd_kernel(const fa_pa
   __shared__ float q_s[kWarpsPerCta][kMaxD];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int bidb = blockIdx.z, bidh = blockIdx.y;
-  const SeqInfo seq(p.cu_seqlens_q, p.cu_seqlens_k, bidb);
+  const SeqInfo seq(p, bidb);
   const int i = blockIdx.x * kWarpsPerCta + warp;   // query row within the sequence
   if (i >= seq.seqlen_q) return;
   const int d = p.d;
   const uint32_t bh = bidb * p.h + bidh;
   const PhiloxKey pk = make_philox_key(p.philox_seed, p.philox_offset);
+  const uint32_t c3 = philox_c3(p, pk);
+  const float slope = p.alibi_slopes != nullptr ? p.alibi_slopes[bidh] : 0.f;   // ALiBi: z = scale*s - slope*|i - j|
   const bool is_dropout = p.p_dropout > 0.f;
   const uint32_t keep_thr = keep_threshold_u16(p.p_dropout);
   const float rp_dropout = 1.f / (1.f - p.p_dropout);
@@ -99,17 +101,18 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) simt_fwd_kernel(const fa_pa
     for (int j0 = 0; j0 < k_end; j0 += 32) {
       const int j = j0 + lane;
       const bool valid = j < k_end && bm.on(i, j);
-      float s = -INFINITY;
+      float s = -INFINITY;   // scaled (and biased) score
       if (valid)
-        s = dot_row<kBf16>(q_s[warp], p.k, (int64_t)(seq.k_begin + j) * p.k_row_stride + (int64_t)bidh * p.k_head_stride, d);
+        s = p.softmax_scale * dot_row<kBf16>(q_s[warp], p.k, (int64_t)(seq.k_begin + j) * p.k_row_stride + (int64_t)bidh * p.k_head_stride, d)
+            - slope * fabsf((float)(i - j));
       const float m_new = fmaxf(m, warp_max(s));
       const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-      const float alpha = __expf(p.softmax_scale * (m - m_use));   // m = -inf -> 0
-      float pr = valid ? __expf(p.softmax_scale * (s - m_use)) : 0.f;
+      const float alpha = __expf(m - m_use);   // m = -inf -> 0
+      float pr = valid ? __expf(s - m_use) : 0.f;
       l = l * alpha + warp_sum(pr);
       m = m_new;
       if (is_dropout && valid) {
-        const uint4 r = dropout_rand8(pk, bh, (uint32_t)i, (uint32_t)j >> 3);
+        const uint4 r = dropout_rand8(pk, c3, bh, (uint32_t)i, (uint32_t)j >> 3);
         if (rand8_get(r, j & 7) > keep_thr) pr = 0.f;
       }
 #pragma unroll
@@ -126,7 +129,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) simt_fwd_kernel(const fa_pa
       }
     }
     const float inv_l = (l == 0.f || l != l) ? 1.f : 1.f / l;
-    lse = (l == 0.f || l != l) ? -INFINITY : m * p.softmax_scale + __logf(l);
+    lse = (l == 0.f || l != l) ? -INFINITY : m + __logf(l);
     if (own) {
       float outv[4];
 #pragma unroll
@@ -148,9 +151,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) simt_fwd_kernel(const fa_pa
       float pr = 0.f;
       if (valid) {
         const float s = dot_row<kBf16>(q_s[warp], p.k, (int64_t)(seq.k_begin + j) * p.k_row_stride + (int64_t)bidh * p.k_head_stride, d);
-        pr = __expf(p.softmax_scale * s - lse);
+        pr = __expf(p.softmax_scale * s - slope * fabsf((float)(i - j)) - lse);
         if (is_dropout) {
-          const uint4 r = dropout_rand8(pk, bh, (uint32_t)i, (uint32_t)j >> 3);
+          const uint4 r = dropout_rand8(pk, c3, bh, (uint32_t)i, (uint32_t)j >> 3);
           // sign bit set <=> dropped (src/fmha/softmax.h:232-234); -0.0 still encodes "dropped"
           if (rand8_get(r, j & 7) > keep_thr) pr = -pr;
         }
@@ -168,7 +171,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) simt_dot_do_o_kernel(const 
   using T = typename Elem<kBf16>::T;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int bidb = blockIdx.z, bidh = blockIdx.y;
-  const SeqInfo seq(p.cu_seqlens_q, p.cu_seqlens_k, bidb);
+  const SeqInfo seq(p, bidb);
   const int i = blockIdx.x * kWarpsPerCta + warp;
   if (i >= p.seqlen_q_rounded) return;
   float acc = 0.f;
@@ -190,12 +193,14 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) simt_bwd_dq_kernel(const fa
   __shared__ float do_s[kWarpsPerCta][kMaxD];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int bidb = blockIdx.z, bidh = blockIdx.y;
-  const SeqInfo seq(p.cu_seqlens_q, p.cu_seqlens_k, bidb);
+  const SeqInfo seq(p, bidb);
   const int i = blockIdx.x * kWarpsPerCta + warp;
   if (i >= seq.seqlen_q) return;
   const int d = p.d;
   const uint32_t bh = bidb * p.h + bidh;
   const PhiloxKey pk = make_philox_key(p.philox_seed, p.philox_offset);
+  const uint32_t c3 = philox_c3(p, pk);
+  const float slope = p.alibi_slopes != nullptr ? p.alibi_slopes[bidh] : 0.f;   // ALiBi: z = scale*s - slope*|i - j|
   const bool is_dropout = p.p_dropout > 0.f;
   const uint32_t keep_thr = keep_threshold_u16(p.p_dropout);
   const float rp_dropout = 1.f / (1.f - p.p_dropout);
@@ -218,9 +223,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) simt_bwd_dq_kernel(const fa
       const int64_t voff = (int64_t)(seq.k_begin + j) * p.v_row_stride + (int64_t)bidh * p.v_head_stride;
       const float s = dot_row<kBf16>(q_s[warp], p.k, koff, d);
       float dp = dot_row<kBf16>(do_s[warp], p.v, voff, d);
-      const float pr = __expf(p.softmax_scale * s - lse);
+      const float pr = __expf(p.softmax_scale * s - slope * fabsf((float)(i - j)) - lse);
       if (is_dropout) {
-        const uint4 r = dropout_rand8(pk, bh, (uint32_t)i, (uint32_t)j >> 3);
+        const uint4 r = dropout_rand8(pk, c3, bh, (uint32_t)i, (uint32_t)j >> 3);
         dp = (rand8_get(r, j & 7) > keep_thr) ? 0.f : dp * rp_dropout;
       }
       ds = pr * (dp - D) * p.softmax_scale;
@@ -248,12 +253,14 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) simt_bwd_dkv_kernel(const f
   __shared__ float v_s[kWarpsPerCta][kMaxD];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int bidb = blockIdx.z, bidh = blockIdx.y;
-  const SeqInfo seq(p.cu_seqlens_q, p.cu_seqlens_k, bidb);
+  const SeqInfo seq(p, bidb);
   const int j = blockIdx.x * kWarpsPerCta + warp;
   if (j >= seq.seqlen_k) return;
   const int d = p.d;
   const uint32_t bh = bidb * p.h + bidh;
   const PhiloxKey pk = make_philox_key(p.philox_seed, p.philox_offset);
+  const uint32_t c3 = philox_c3(p, pk);
+  const float slope = p.alibi_slopes != nullptr ? p.alibi_slopes[bidh] : 0.f;   // ALiBi: z = scale*s - slope*|i - j|
   const bool is_dropout = p.p_dropout > 0.f;
   const uint32_t keep_thr = keep_threshold_u16(p.p_dropout);
   const float rp_dropout = 1.f / (1.f - p.p_dropout);
@@ -277,10 +284,10 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) simt_bwd_dkv_kernel(const f
         const int64_t gooff = (int64_t)(seq.q_begin + i) * p.do_row_stride + (int64_t)bidh * p.do_head_stride;
         const float s = dot_row<kBf16>(k_s[warp], p.q, qoff, d);
         float dp = dot_row<kBf16>(v_s[warp], p.dout, gooff, d);
-        const float pr = __expf(p.softmax_scale * s - lse);
+        const float pr = __expf(p.softmax_scale * s - slope * fabsf((float)(i - j)) - lse);
         pd = pr;
         if (is_dropout) {
-          const uint4 r = dropout_rand8(pk, bh, (uint32_t)i, (uint32_t)j >> 3);
+          const uint4 r = dropout_rand8(pk, c3, bh, (uint32_t)i, (uint32_t)j >> 3);
           const bool keep = rand8_get(r, j & 7) <= keep_thr;
           dp = keep ? dp * rp_dropout : 0.f;
           pd = keep ? pr * rp_dropout : 0.f;

@@ -21,47 +21,31 @@ def _get_block_size(device, head_dim, is_dropout):
 
 
 def _flash_attn_forward(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, dropout_p,
-                        softmax_scale, causal, return_softmax):
-    """reference :17-26"""
-    res = flash_attn_cuda.fwd(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, dropout_p,
-                              softmax_scale, False, causal, return_softmax, None)
-    return res[0], res[1], (res[2] if return_softmax else None)
+                        softmax_scale, causal, return_softmax, alibi_slopes=None):
+    """reference :17-26.  -> out, softmax_lse, S_dmask or None, and the dropout stream the call used (handed to the
+    backward instead of the reference's global RNG-state round trip, reference :44, :61-63)."""
+    res, rng = flash_attn_cuda.fwd_ex(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, dropout_p,
+                                      softmax_scale, causal, return_softmax, None, alibi_slopes=alibi_slopes)
+    return res[0], res[1], (res[2] if return_softmax else None), rng
 
 
 def _flash_attn_backward(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seqlens_k,
-                         max_seqlen_q, max_seqlen_k, dropout_p, softmax_scale, causal):
+                         max_seqlen_q, max_seqlen_k, dropout_p, softmax_scale, causal, rng=None, alibi_slopes=None):
     """reference :29-36"""
     softmax_d = flash_attn_cuda.bwd(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seqlens_k,
-                                    max_seqlen_q, max_seqlen_k, dropout_p, softmax_scale, False, causal, None)
+                                    max_seqlen_q, max_seqlen_k, dropout_p, softmax_scale, False, causal, rng,
+                                    alibi_slopes=alibi_slopes)
     return dq, dk, dv, softmax_d
-
-
-class _RngReplay:
-    """The reference's dropout protocol (reference :44, :61-63, :70-71): remember the CUDA RNG state seen by the
-    forward, and re-install it around the backward so the native side draws the same (seed, offset)."""
-
-    def __init__(self, dropout_p):
-        self.state = torch.cuda.get_rng_state() if dropout_p > 0 else None
-
-    def __enter__(self):
-        if self.state is not None:
-            self.current = torch.cuda.get_rng_state()
-            torch.cuda.set_rng_state(self.state)
-
-    def __exit__(self, *exc):
-        if self.state is not None:
-            torch.cuda.set_rng_state(self.current)
-        return False
 
 
 def _default_scale(softmax_scale, head_dim):
     return head_dim ** (-0.5) if softmax_scale is None else softmax_scale
 
 
-def _save_hparams(ctx, dropout_p, max_seqlen_q, max_seqlen_k, softmax_scale, causal, rng):
+def _save_hparams(ctx, dropout_p, max_seqlen_q, max_seqlen_k, softmax_scale, causal, rng, alibi_slopes):
     ctx.dropout_p, ctx.softmax_scale, ctx.causal = dropout_p, softmax_scale, causal
     ctx.max_seqlen_q, ctx.max_seqlen_k = max_seqlen_q, max_seqlen_k
-    ctx.rng = rng
+    ctx.rng, ctx.alibi_slopes = rng, alibi_slopes
 
 
 class FlashAttnQKVPackedFunc(torch.autograd.Function):
@@ -69,25 +53,23 @@ class FlashAttnQKVPackedFunc(torch.autograd.Function):
     straight into views of one packed dqkv (reference :39-72)."""
 
     @staticmethod
-    def forward(ctx, qkv, cu_seqlens, max_seqlen, dropout_p, softmax_scale, causal, return_softmax):
-        rng = _RngReplay(dropout_p)
+    def forward(ctx, qkv, cu_seqlens, max_seqlen, dropout_p, softmax_scale, causal, return_softmax, alibi_slopes=None):
         softmax_scale = _default_scale(softmax_scale, qkv.shape[-1])
-        out, lse, s_dmask = _flash_attn_forward(qkv[:, 0], qkv[:, 1], qkv[:, 2], cu_seqlens, cu_seqlens,
-                                                max_seqlen, max_seqlen, dropout_p, softmax_scale, causal,
-                                                return_softmax)
+        out, lse, s_dmask, rng = _flash_attn_forward(qkv[:, 0], qkv[:, 1], qkv[:, 2], cu_seqlens, cu_seqlens,
+                                                     max_seqlen, max_seqlen, dropout_p, softmax_scale, causal,
+                                                     return_softmax, alibi_slopes)
         ctx.save_for_backward(qkv, out, lse, cu_seqlens)
-        _save_hparams(ctx, dropout_p, max_seqlen, max_seqlen, softmax_scale, causal, rng)
+        _save_hparams(ctx, dropout_p, max_seqlen, max_seqlen, softmax_scale, causal, rng, alibi_slopes)
         return (out, lse, s_dmask) if return_softmax else out
 
     @staticmethod
     def backward(ctx, dout, *unused):
         qkv, out, lse, cu_seqlens = ctx.saved_tensors
         dqkv = torch.empty_like(qkv)
-        with ctx.rng:
-            _flash_attn_backward(dout, qkv[:, 0], qkv[:, 1], qkv[:, 2], out, lse, dqkv[:, 0], dqkv[:, 1],
-                                 dqkv[:, 2], cu_seqlens, cu_seqlens, ctx.max_seqlen_q, ctx.max_seqlen_k,
-                                 ctx.dropout_p, ctx.softmax_scale, ctx.causal)
-        return dqkv, None, None, None, None, None, None
+        _flash_attn_backward(dout, qkv[:, 0], qkv[:, 1], qkv[:, 2], out, lse, dqkv[:, 0], dqkv[:, 1],
+                             dqkv[:, 2], cu_seqlens, cu_seqlens, ctx.max_seqlen_q, ctx.max_seqlen_k,
+                             ctx.dropout_p, ctx.softmax_scale, ctx.causal, ctx.rng, ctx.alibi_slopes)
+        return dqkv, None, None, None, None, None, None, None
 
 
 class FlashAttnKVPackedFunc(torch.autograd.Function):
@@ -95,24 +77,23 @@ class FlashAttnKVPackedFunc(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, q, kv, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, dropout_p, softmax_scale,
-                causal, return_softmax):
-        rng = _RngReplay(dropout_p)
+                causal, return_softmax, alibi_slopes=None):
         softmax_scale = _default_scale(softmax_scale, q.shape[-1])
-        out, lse, s_dmask = _flash_attn_forward(q, kv[:, 0], kv[:, 1], cu_seqlens_q, cu_seqlens_k, max_seqlen_q,
-                                                max_seqlen_k, dropout_p, softmax_scale, causal, return_softmax)
+        out, lse, s_dmask, rng = _flash_attn_forward(q, kv[:, 0], kv[:, 1], cu_seqlens_q, cu_seqlens_k, max_seqlen_q,
+                                                     max_seqlen_k, dropout_p, softmax_scale, causal, return_softmax,
+                                                     alibi_slopes)
         ctx.save_for_backward(q, kv, out, lse, cu_seqlens_q, cu_seqlens_k)
-        _save_hparams(ctx, dropout_p, max_seqlen_q, max_seqlen_k, softmax_scale, causal, rng)
+        _save_hparams(ctx, dropout_p, max_seqlen_q, max_seqlen_k, softmax_scale, causal, rng, alibi_slopes)
         return (out, lse, s_dmask) if return_softmax else out
 
     @staticmethod
     def backward(ctx, dout, *unused):
         q, kv, out, lse, cu_seqlens_q, cu_seqlens_k = ctx.saved_tensors
         dq, dkv = torch.empty_like(q), torch.empty_like(kv)
-        with ctx.rng:
-            _flash_attn_backward(dout, q, kv[:, 0], kv[:, 1], out, lse, dq, dkv[:, 0], dkv[:, 1], cu_seqlens_q,
-                                 cu_seqlens_k, ctx.max_seqlen_q, ctx.max_seqlen_k, ctx.dropout_p,
-                                 ctx.softmax_scale, ctx.causal)
-        return dq, dkv, None, None, None, None, None, None, None, None
+        _flash_attn_backward(dout, q, kv[:, 0], kv[:, 1], out, lse, dq, dkv[:, 0], dkv[:, 1], cu_seqlens_q,
+                             cu_seqlens_k, ctx.max_seqlen_q, ctx.max_seqlen_k, ctx.dropout_p,
+                             ctx.softmax_scale, ctx.causal, ctx.rng, ctx.alibi_slopes)
+        return dq, dkv, None, None, None, None, None, None, None, None, None
 
 
 class FlashAttnFunc(torch.autograd.Function):
@@ -120,27 +101,26 @@ class FlashAttnFunc(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, dropout_p, softmax_scale,
-                causal, return_softmax):
-        rng = _RngReplay(dropout_p)
+                causal, return_softmax, alibi_slopes=None):
         softmax_scale = _default_scale(softmax_scale, q.shape[-1])
-        out, lse, s_dmask = _flash_attn_forward(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k,
-                                                dropout_p, softmax_scale, causal, return_softmax)
+        out, lse, s_dmask, rng = _flash_attn_forward(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k,
+                                                     dropout_p, softmax_scale, causal, return_softmax, alibi_slopes)
         ctx.save_for_backward(q, k, v, out, lse, cu_seqlens_q, cu_seqlens_k)
-        _save_hparams(ctx, dropout_p, max_seqlen_q, max_seqlen_k, softmax_scale, causal, rng)
+        _save_hparams(ctx, dropout_p, max_seqlen_q, max_seqlen_k, softmax_scale, causal, rng, alibi_slopes)
         return (out, lse, s_dmask) if return_softmax else out
 
     @staticmethod
     def backward(ctx, dout, *unused):
         q, k, v, out, lse, cu_seqlens_q, cu_seqlens_k = ctx.saved_tensors
         dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
-        with ctx.rng:
-            _flash_attn_backward(dout, q, k, v, out, lse, dq, dk, dv, cu_seqlens_q, cu_seqlens_k,
-                                 ctx.max_seqlen_q, ctx.max_seqlen_k, ctx.dropout_p, ctx.softmax_scale, ctx.causal)
-        return dq, dk, dv, None, None, None, None, None, None, None, None
+        _flash_attn_backward(dout, q, k, v, out, lse, dq, dk, dv, cu_seqlens_q, cu_seqlens_k,
+                             ctx.max_seqlen_q, ctx.max_seqlen_k, ctx.dropout_p, ctx.softmax_scale, ctx.causal,
+                             ctx.rng, ctx.alibi_slopes)
+        return dq, dk, dv, None, None, None, None, None, None, None, None, None
 
 
 def flash_attn_unpadded_qkvpacked_func(qkv, cu_seqlens, max_seqlen, dropout_p, softmax_scale=None, causal=False,
-                                       return_attn_probs=False):
+                                       return_attn_probs=False, alibi_slopes=None):
     """Self-attention on a packed varlen batch (reference :151-176).  dropout_p must be 0.0 at evaluation.
 
     qkv: (total, 3, nheads, headdim); cu_seqlens: (batch + 1,) int32 cumulative lengths; max_seqlen: int.
@@ -148,25 +128,27 @@ def flash_attn_unpadded_qkvpacked_func(qkv, cu_seqlens, max_seqlen, dropout_p, s
     Returns out (total, nheads, headdim); with return_attn_probs=True (testing only) also
     softmax_lse (batch, nheads, round16(max_seqlen)) fp32 and S_dmask (batch, nheads, sq_rounded, sk_rounded):
     softmax probabilities in natural layout, NEGATIVE where the position was dropped.
+    alibi_slopes (extension, the reference's roadmap item README.md:57): fp32 (nheads,) tensor; adds the bias
+    -slope[h] * |i - j| to the scaled scores (no gradient flows to the slopes).
     """
     return FlashAttnQKVPackedFunc.apply(qkv, cu_seqlens, max_seqlen, dropout_p, softmax_scale, causal,
-                                        return_attn_probs)
+                                        return_attn_probs, alibi_slopes)
 
 
 def flash_attn_unpadded_kvpacked_func(q, kv, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, dropout_p,
-                                      softmax_scale=None, causal=False, return_attn_probs=False):
+                                      softmax_scale=None, causal=False, return_attn_probs=False, alibi_slopes=None):
     """q: (total_q, nheads, headdim), kv: (total_k, 2, nheads, headdim) (reference :179-210).  See
     flash_attn_unpadded_qkvpacked_func for the remaining arguments and the return value."""
     return FlashAttnKVPackedFunc.apply(q, kv, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, dropout_p,
-                                       softmax_scale, causal, return_attn_probs)
+                                       softmax_scale, causal, return_attn_probs, alibi_slopes)
 
 
 def flash_attn_unpadded_func(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, dropout_p,
-                             softmax_scale=None, causal=False, return_attn_probs=False):
+                             softmax_scale=None, causal=False, return_attn_probs=False, alibi_slopes=None):
     """q: (total_q, nheads, headdim), k and v: (total_k, nheads, headdim) (reference :213-243).  See
     flash_attn_unpadded_qkvpacked_func for the remaining arguments and the return value."""
     return FlashAttnFunc.apply(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, dropout_p,
-                               softmax_scale, causal, return_attn_probs)
+                               softmax_scale, causal, return_attn_probs, alibi_slopes)
 
 
 def flash_attn_func(qkv, cu_seqlens, dropout_p, max_s, softmax_scale=None, causal=False, return_attn_probs=False):

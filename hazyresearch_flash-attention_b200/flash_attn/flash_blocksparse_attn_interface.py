@@ -31,16 +31,16 @@ def convert_blockmask(blockmask, causal):
 def _flash_blocksparse_attn_forward(qkv, cu_seqlens, blockmask, dropout_p, max_s, softmax_scale, causal,
                                      return_softmax):
     """reference :43-51"""
-    res = flash_attn_cuda.fwd_block(qkv, cu_seqlens, blockmask, dropout_p, max_s, softmax_scale, causal,
-                                    return_softmax, None)
-    return res[0], res[1], (res[2] if return_softmax else None)
+    res, rng = flash_attn_cuda.fwd_block_ex(qkv, cu_seqlens, blockmask, dropout_p, max_s, softmax_scale, causal,
+                                            return_softmax, None)
+    return res[0], res[1], (res[2] if return_softmax else None), rng
 
 
 def _flash_blocksparse_attn_backward(dout, qkv, out, S_dmask, softmax_lse, cu_seqlens, blockmask, dropout_p, max_s,
-                                      softmax_scale, causal):
+                                      softmax_scale, causal, rng=None):
     """reference :54-61 (bwd_block takes softmax_scale BEFORE max_s)"""
     dqkv, dp, softmax_d = flash_attn_cuda.bwd_block(dout, qkv, out, S_dmask, softmax_lse, cu_seqlens, blockmask,
-                                                    dropout_p, softmax_scale, max_s, causal, None)
+                                                    dropout_p, softmax_scale, max_s, causal, rng)
     return dqkv
 
 
@@ -48,27 +48,22 @@ class _BlocksparseBase(torch.autograd.Function):
 
     @staticmethod
     def _fwd(ctx, qkv, cu_seqlens, blockmask, dropout_p, max_s, softmax_scale, causal, return_softmax):
-        rng_state = torch.cuda.get_rng_state() if dropout_p > 0 else None   # backward regenerates the mask
         if softmax_scale is None:
             softmax_scale = qkv.shape[-1] ** (-0.5)
-        context, softmax_lse, S_dmask = _flash_blocksparse_attn_forward(
+        # rng: the dropout stream of this call; the backward regenerates the mask from it (the reference saves and
+        # restores the global CUDA RNG state instead, reference :72, :85-90)
+        context, softmax_lse, S_dmask, rng = _flash_blocksparse_attn_forward(
             qkv, cu_seqlens, blockmask, dropout_p, max_s, softmax_scale, causal=causal, return_softmax=return_softmax)
-        ctx.save_for_backward(qkv, context, S_dmask, softmax_lse, cu_seqlens, blockmask, rng_state)
-        ctx.dropout_p, ctx.max_s, ctx.softmax_scale, ctx.causal = dropout_p, max_s, softmax_scale, causal
+        ctx.save_for_backward(qkv, context, S_dmask, softmax_lse, cu_seqlens, blockmask)
+        ctx.dropout_p, ctx.max_s, ctx.softmax_scale, ctx.causal, ctx.rng = dropout_p, max_s, softmax_scale, causal, rng
         return context, S_dmask, softmax_lse
 
     @staticmethod
     def _bwd(ctx, dout):
-        qkv, context, S_dmask, softmax_lse, cu_seqlens, blockmask, rng_state = ctx.saved_tensors
-        if rng_state is not None:
-            cur_rng_state = torch.cuda.get_rng_state()
-            torch.cuda.set_rng_state(rng_state)
-        dqkv = _flash_blocksparse_attn_backward(dout, qkv, context, S_dmask if S_dmask is not None else context,
+        qkv, context, S_dmask, softmax_lse, cu_seqlens, blockmask = ctx.saved_tensors
+        return _flash_blocksparse_attn_backward(dout, qkv, context, S_dmask if S_dmask is not None else context,
                                                 softmax_lse, cu_seqlens, blockmask, ctx.dropout_p, ctx.max_s,
-                                                ctx.softmax_scale, ctx.causal)
-        if rng_state is not None:
-            torch.cuda.set_rng_state(cur_rng_state)
-        return dqkv
+                                                ctx.softmax_scale, ctx.causal, ctx.rng)
 
 
 class FlashBlocksparseAttnFun(torch.autograd.Function):

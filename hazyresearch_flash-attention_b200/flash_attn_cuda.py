@@ -19,14 +19,11 @@ _LIB_PATH = os.environ.get("FA_B200_LIB") or os.path.join(_HERE, "csrc", "libfa_
 FA_IMPL_AUTO, FA_IMPL_TCGEN05, FA_IMPL_SIMT = 0, 1, 2
 FA_OP_FWD, FA_OP_BWD, FA_OP_FWD_BLOCK, FA_OP_BWD_BLOCK = 0, 1, 2, 3
 
-# Kernel selection for debugging / cross-checks (FA_IMPL_*).  Tests flip this; users never need to.
-_impl = int(os.environ.get("FA_B200_IMPL", FA_IMPL_AUTO))
+FA_FLAG_WS_ZEROED = 1
 
-
-def set_impl(impl):
-    global _impl
-    old, _impl = _impl, int(impl)
-    return old
+# fa_params.impl of every call.  Always FA_IMPL_AUTO (the tcgen05 kernels) in the product; the GPU test-suite patches
+# this module attribute to FA_IMPL_SIMT to cross-check against the library's CUDA-core kernels (tests/fa_test_utils.py).
+_impl = FA_IMPL_AUTO
 
 
 class FaParams(ctypes.Structure):
@@ -36,6 +33,7 @@ class FaParams(ctypes.Structure):
             "q", "k", "v", "o", "dout", "dq", "dk", "dv", "softmax_lse", "softmax_d", "s_dmask",
             "cu_seqlens_q", "cu_seqlens_k", "blockmask", "workspace")]
         + [("workspace_bytes", ctypes.c_uint64)]
+        + [(n, ctypes.c_void_p) for n in ("seqused_q", "seqused_k", "alibi_slopes", "philox_offset_ptr")]
         + [(n, ctypes.c_int64) for n in (
             "q_row_stride", "q_head_stride", "k_row_stride", "k_head_stride", "v_row_stride", "v_head_stride",
             "o_row_stride", "o_head_stride", "do_row_stride", "do_head_stride", "dq_row_stride", "dq_head_stride",
@@ -44,7 +42,7 @@ class FaParams(ctypes.Structure):
             "b", "h", "d", "total_q", "total_k", "max_seqlen_q", "max_seqlen_k", "seqlen_q_rounded",
             "seqlen_k_rounded", "blockmask_nrow", "blockmask_ncol")]
         + [("softmax_scale", ctypes.c_float), ("p_dropout", ctypes.c_float)]
-        + [(n, ctypes.c_int32) for n in ("is_causal", "is_bf16", "impl", "reserved0")]
+        + [(n, ctypes.c_int32) for n in ("is_causal", "is_bf16", "impl")] + [("flags", ctypes.c_uint32)]
         + [("philox_seed", ctypes.c_uint64), ("philox_offset", ctypes.c_uint64)]
     )
 
@@ -70,16 +68,23 @@ def _load_library():
         fn.restype = ctypes.c_int
         fn.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64,
                        ctypes.c_void_p]
+    lib.fa_workspace_zero_range.restype = ctypes.c_uint64
+    lib.fa_workspace_zero_range.argtypes = [ctypes.POINTER(FaParams), ctypes.c_int, ctypes.POINTER(ctypes.c_uint64)]
+    lib.fa_philox_advance.restype = ctypes.c_int
+    lib.fa_philox_advance.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p]
     lib.fa_merge_partials.restype = ctypes.c_int
-    lib.fa_merge_partials.argtypes = [ctypes.c_void_p] * 5 + [ctypes.c_int32] * 8 + [ctypes.c_void_p]
+    lib.fa_merge_partials.argtypes = ([ctypes.c_void_p] * 4 + [ctypes.c_int32] * 4 + [ctypes.c_int64] + [ctypes.c_int32] * 4
+                                      + [ctypes.c_void_p])
+    lib.fa_accumulate_f32.restype = ctypes.c_int
+    lib.fa_accumulate_f32.argtypes = [ctypes.c_void_p, ctypes.c_void_p] + [ctypes.c_int64] * 4 + [ctypes.c_int32, ctypes.c_void_p]
     lib.fa_rotary_qk.restype = ctypes.c_int
     lib.fa_rotary_qk.argtypes = ([ctypes.c_void_p] * 4 + [ctypes.c_int64] + [ctypes.c_int32] * 5 + [ctypes.c_int64] * 2
                                  + [ctypes.c_int32] * 2 + [ctypes.c_void_p])
     lib.fa_dropout_keep8_host.restype = None
     lib.fa_dropout_keep8_host.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint32,
                                           ctypes.c_uint32, ctypes.c_float, ctypes.c_void_p]
-    if lib.fa_abi_version() != 1:
-        raise ImportError(f"{_LIB_PATH}: ABI version {lib.fa_abi_version()} != 1")
+    if lib.fa_abi_version() != 2:
+        raise ImportError(f"{_LIB_PATH}: ABI version {lib.fa_abi_version()} != 2")
     lib.fa_sizeof_params.restype = ctypes.c_uint64
     lib.fa_launch_count.restype = ctypes.c_uint64
     lib.fa_timing_enable.restype = None
@@ -161,26 +166,61 @@ def _check_qkv_itemised(q, k, v, cu_seqlens_q, cu_seqlens_k):
     return batch_size, total_q, total_k, num_heads, head_size
 
 
-def _philox_state(p_dropout, gen, device, params):
-    """(seed, offset) for this call; advances the generator like at::CUDAGeneratorImpl::philox_cuda_state
+class PhiloxState:
+    """The dropout stream of ONE forward call: (seed, offset) host integers and, for a call captured in a CUDA graph,
+    the device counter the kernels add to the offset.  A forward hands it to its backward (as `gen`), which therefore
+    regenerates exactly the same mask -- on any device, without touching the global RNG state."""
+    __slots__ = ("seed", "offset", "counter")
+
+    def __init__(self, seed, offset, counter=None):
+        self.seed, self.offset, self.counter = seed, offset, counter
+
+
+# Graph-capturable dropout: per device (seed, base offset, int64[1] device counter).  The CUDA generator cannot be
+# queried during capture, so a captured forward takes the cached seed and lets a one-thread kernel hand out the
+# counter (fa_philox_advance): every replay of the graph then draws a fresh mask, like the reference's
+# PhiloxCudaState (csrc/flash_attn/src/fmha.h:39).  Filled by the first uncaptured dropout call on the device.
+_graph_rng = {}
+
+
+def _philox_state(p_dropout, gen, device, params, raw_stream):
+    """-> PhiloxState or None.  Advances the generator like at::CUDAGeneratorImpl::philox_cuda_state
     (fmha_api.cpp:228-235).  No RNG state is touched when p_dropout == 0 (fmha_api.cpp:231)."""
     if p_dropout <= 0.0:
-        return 0, 0
-    # The (seed, offset) pair is read on the host: under CUDA-graph capture it would be frozen into the graph and every
-    # replay would draw the same mask (the reference's PhiloxCudaState reads a device-side offset instead, fmha.h:39).
-    _check(not torch.cuda.is_current_stream_capturing(),
-           "dropout under CUDA graph capture is not supported (capture with p_dropout = 0)")
+        return None
+    if isinstance(gen, PhiloxState):
+        return gen
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    inc = int(_lib.fa_philox_increment(ctypes.byref(params)))
+    if torch.cuda.is_current_stream_capturing():
+        st = _graph_rng.get(idx)
+        _check(st is not None, "dropout under CUDA graph capture needs one uncaptured dropout call on this device first "
+                               "(the usual warm-up iteration): it creates the device-side Philox counter")
+        counter = torch.empty(1, dtype=torch.int64, device=device)
+        _raise_if_failed(_lib.fa_philox_advance(st[2].data_ptr(), counter.data_ptr(), inc, raw_stream), "fa_philox_advance")
+        return PhiloxState(st[0], st[1], counter)
     if gen is None:
-        idx = device.index if device.index is not None else torch.cuda.current_device()
         gen = torch.cuda.default_generators[idx]
-    seed = gen.initial_seed()
+    seed = gen.initial_seed() & 0xFFFFFFFFFFFFFFFF
     offset = gen.get_offset()
-    gen.set_offset(offset + int(_lib.fa_philox_increment(ctypes.byref(params))))
-    return seed & 0xFFFFFFFFFFFFFFFF, offset
+    gen.set_offset(offset + inc)
+    st = _graph_rng.get(idx)
+    if st is None:
+        _graph_rng[idx] = [seed, offset, torch.zeros(1, dtype=torch.int64, device=device)]
+    else:
+        st[0], st[1] = seed, offset
+    return PhiloxState(seed, offset)
+
+
+def _set_philox(P, state):
+    if state is not None:
+        P.philox_seed, P.philox_offset = state.seed, state.offset
+        if state.counter is not None:
+            P.philox_offset_ptr = state.counter.data_ptr()
 
 
 def _fill_common(P, q, k, v, cu_seqlens_q, cu_seqlens_k, b, h, d, total_q, total_k, max_seqlen_q, max_seqlen_k,
-                 p_dropout, softmax_scale, is_causal):
+                 p_dropout, softmax_scale, is_causal, seqused_q=None, seqused_k=None, alibi_slopes=None):
     P.q, P.k, P.v = q.data_ptr(), k.data_ptr(), v.data_ptr()
     P.q_row_stride, P.q_head_stride, _ = q.stride()
     P.k_row_stride, P.k_head_stride, _ = k.stride()
@@ -194,6 +234,16 @@ def _fill_common(P, q, k, v, cu_seqlens_q, cu_seqlens_k, b, h, d, total_q, total
     P.is_causal = 1 if is_causal else 0
     P.is_bf16 = 1 if q.dtype == torch.bfloat16 else 0
     P.impl = _impl
+    if seqused_q is not None or seqused_k is not None or alibi_slopes is not None:
+        for name, t in (("seqused_q", seqused_q), ("seqused_k", seqused_k)):
+            if t is not None:
+                _check(t.is_cuda and t.dtype == torch.int32 and t.is_contiguous() and t.numel() == b,
+                       f"{name} must be a contiguous int32 CUDA tensor of batch_size elements")
+                setattr(P, name, t.data_ptr())
+        if alibi_slopes is not None:
+            _check(alibi_slopes.is_cuda and alibi_slopes.dtype == torch.float32 and alibi_slopes.is_contiguous()
+                   and alibi_slopes.numel() == h, "alibi_slopes must be a contiguous fp32 CUDA tensor of nheads elements")
+            P.alibi_slopes = alibi_slopes.data_ptr()
 
 
 class _DeviceGuard:
@@ -206,39 +256,71 @@ class _DeviceGuard:
         self.prev = -1
 
     def __enter__(self):
-        cur = torch._C._cuda_getDevice()
+        cur = _current_device()
         if self.idx is not None and self.idx != cur:
             self.prev = cur
-            torch._C._cuda_setDevice(self.idx)
+            _set_device(self.idx)
         elif self.idx is None:
             self.idx = cur
         return self
 
     def __exit__(self, *exc):
         if self.prev >= 0:
-            torch._C._cuda_setDevice(self.prev)
+            _set_device(self.prev)
         return False
 
     def raw_stream(self):
-        return torch._C._cuda_getCurrentRawStream(self.idx)   # at::cuda::getCurrentCUDAStream(), fmha_api.cpp:132
+        return _raw_stream(self.idx)   # at::cuda::getCurrentCUDAStream(), fmha_api.cpp:132
 
 
-def _workspace(P, op, device):
+# the private fast paths of torch.cuda when this torch has them, the public API otherwise
+_current_device = getattr(torch._C, "_cuda_getDevice", None) or torch.cuda.current_device
+_set_device = getattr(torch._C, "_cuda_setDevice", None) or torch.cuda.set_device
+if hasattr(torch._C, "_cuda_getCurrentRawStream"):
+    _raw_stream = torch._C._cuda_getCurrentRawStream
+else:
+    def _raw_stream(idx):
+        return torch.cuda.current_stream(idx).cuda_stream
+
+
+# Backward scratch kept per (device, stream): [tensor, dirty_lo, dirty_hi].  The library leaves the fp32 dQ accumulator
+# and its counters (the head of the workspace, fa_workspace_zero_range) all-zero when a backward completes, so a kept
+# buffer is cleared once at allocation and never again (FA_FLAG_WS_ZEROED) -- no 400 MB memset per call at the headline
+# size.  [dirty_lo, dirty_hi) tracks the statistics area behind the zero range, which moves when the sizes change.
+_ws_cache = {}
+
+
+def _workspace(P, op, device, raw_stream=None):
     nbytes = int(_lib.fa_workspace_bytes(ctypes.byref(P), op))
     if nbytes == 0:
         return None
-    ws = torch.empty(nbytes, dtype=torch.uint8, device=device)
+    if op != FA_OP_BWD or raw_stream is None or torch.cuda.is_current_stream_capturing():
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=device)      # the library clears what it needs
+        P.workspace, P.workspace_bytes = ws.data_ptr(), nbytes
+        return ws
+    zlen = int(_lib.fa_workspace_zero_range(ctypes.byref(P), op, None))  # the range starts at byte 0 for FA_OP_BWD
+    key = (device.index, raw_stream)
+    ent = _ws_cache.get(key)
+    if ent is None or ent[0].numel() < nbytes:
+        ent = _ws_cache[key] = [torch.zeros(nbytes, dtype=torch.uint8, device=device), nbytes, nbytes]
+    ws, lo, hi = ent
+    if zlen > lo:                       # an earlier, smaller call left statistics where this call accumulates
+        ws[lo:min(hi, zlen)].zero_()
+    ent[1], ent[2] = zlen, (max(hi, nbytes) if hi > zlen else nbytes)
     P.workspace, P.workspace_bytes = ws.data_ptr(), nbytes
+    P.flags |= FA_FLAG_WS_ZEROED
     return ws
 
 
 def _fwd_impl(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, p_dropout, softmax_scale,
-              zero_tensors, is_causal, return_softmax, gen, blockmask=None):
+              zero_tensors, is_causal, return_softmax, gen, blockmask=None, seqused_q=None, seqused_k=None,
+              alibi_slopes=None):
+    """-> ([o, lse (, s)], PhiloxState or None)"""
     b, total_q, total_k, h, d = _check_qkv(q, k, v, cu_seqlens_q, cu_seqlens_k)
     _check(p_dropout < 1.0, "p_dropout must be < 1")
     P = FaParams()
     _fill_common(P, q, k, v, cu_seqlens_q, cu_seqlens_k, b, h, d, total_q, total_k, int(max_seqlen_q),
-                 int(max_seqlen_k), float(p_dropout), float(softmax_scale), is_causal)
+                 int(max_seqlen_k), float(p_dropout), float(softmax_scale), is_causal, seqused_q, seqused_k, alibi_slopes)
     with _DeviceGuard(q.device) as guard:
         o = torch.empty((total_q, h, d), dtype=q.dtype, device=q.device)
         lse = torch.empty((b, h, P.seqlen_q_rounded), dtype=torch.float32, device=q.device)
@@ -259,17 +341,20 @@ def _fwd_impl(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, p
             P.blockmask = blockmask.data_ptr()
             P.blockmask_ncol, P.blockmask_nrow = blockmask.shape
             op = FA_OP_FWD_BLOCK
+        stream = guard.raw_stream()
         ws = _workspace(P, op, q.device)
-        P.philox_seed, P.philox_offset = _philox_state(p_dropout, gen, q.device, P)
+        state = _philox_state(p_dropout, gen, q.device, P, stream)
+        _set_philox(P, state)
         # the workspace is allocated and consumed on the current stream: the caching allocator's same-stream reuse
         # rule already orders any later owner after this kernel
         fn = _lib.fa_fwd if blockmask is None else _lib.fa_fwd_block
-        _raise_if_failed(fn(ctypes.byref(P), guard.raw_stream()), "flash_attn_cuda.fwd")
-    return [o, lse] + ([s] if return_softmax else [])
+        _raise_if_failed(fn(ctypes.byref(P), stream), "flash_attn_cuda.fwd")
+    return [o, lse] + ([s] if return_softmax else []), state
 
 
 def _bwd_impl(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seqlens_k, max_seqlen_q,
-              max_seqlen_k, p_dropout, softmax_scale, zero_tensors, is_causal, gen, blockmask=None):
+              max_seqlen_k, p_dropout, softmax_scale, zero_tensors, is_causal, gen, blockmask=None, seqused_q=None,
+              seqused_k=None, alibi_slopes=None):
     b, total_q, total_k, h, d = _check_qkv(q, k, v, cu_seqlens_q, cu_seqlens_k)
     dt, q_shape, k_shape = q.dtype, (total_q, h, d), (total_k, h, d)
     if not (dout.is_cuda and out.is_cuda and dq.is_cuda and dk.is_cuda and dv.is_cuda
@@ -292,7 +377,7 @@ def _bwd_impl(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seql
         out = out.contiguous()
     P = FaParams()
     _fill_common(P, q, k, v, cu_seqlens_q, cu_seqlens_k, b, h, d, total_q, total_k, int(max_seqlen_q),
-                 int(max_seqlen_k), float(p_dropout), float(softmax_scale), is_causal)
+                 int(max_seqlen_k), float(p_dropout), float(softmax_scale), is_causal, seqused_q, seqused_k, alibi_slopes)
     _check(tuple(softmax_lse.shape) == (b, h, P.seqlen_q_rounded), "softmax_lse has the wrong shape")
     with _DeviceGuard(q.device) as guard:
         softmax_d = torch.empty((b, h, P.seqlen_q_rounded), dtype=torch.float32, device=q.device)
@@ -309,10 +394,11 @@ def _bwd_impl(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seql
             P.blockmask = blockmask.data_ptr()
             P.blockmask_ncol, P.blockmask_nrow = blockmask.shape
             op = FA_OP_BWD_BLOCK
-        ws = _workspace(P, op, q.device)
-        P.philox_seed, P.philox_offset = _philox_state(p_dropout, gen, q.device, P)
+        stream = guard.raw_stream()
+        ws = _workspace(P, op, q.device, stream)
+        _set_philox(P, _philox_state(p_dropout, gen, q.device, P, stream))
         fn = _lib.fa_bwd if blockmask is None else _lib.fa_bwd_block
-        _raise_if_failed(fn(ctypes.byref(P), guard.raw_stream()), "flash_attn_cuda.bwd")
+        _raise_if_failed(fn(ctypes.byref(P), stream), "flash_attn_cuda.bwd")
     return softmax_d
 
 
@@ -326,15 +412,29 @@ def fwd(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, p_dropo
     it is the natural (b, h, sq_rounded, sk_rounded) matrix of +-P with P = exp(scale*s - lse) (true
     probabilities), sign bit set where the position was dropped."""
     return _fwd_impl(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, p_dropout,
-                     softmax_scale, zero_tensors, is_causal, return_softmax, gen)
+                     softmax_scale, zero_tensors, is_causal, return_softmax, gen)[0]
+
+
+def fwd_ex(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, p_dropout, softmax_scale, is_causal,
+           return_softmax=False, gen=None, seqused_q=None, seqused_k=None, alibi_slopes=None):
+    """`fwd` plus what the reference extension does not have: -> ([o, lse (, s_dmask)], PhiloxState or None).
+    The PhiloxState names the dropout stream this call used; pass it to `bwd` as `gen` (no global RNG round trip,
+    works under CUDA-graph capture).  seqused_q / seqused_k: int32 (batch,) row counts that replace the
+    cu_seqlens differences (sequences may then leave gaps); alibi_slopes: fp32 (nheads,), additive bias
+    -slope * |i - j| on the scaled scores."""
+    return _fwd_impl(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, p_dropout, softmax_scale,
+                     False, is_causal, return_softmax, gen, seqused_q=seqused_q, seqused_k=seqused_k,
+                     alibi_slopes=alibi_slopes)
 
 
 def bwd(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k,
-        p_dropout, softmax_scale, zero_tensors, is_causal, gen=None):
+        p_dropout, softmax_scale, zero_tensors, is_causal, gen=None, seqused_q=None, seqused_k=None,
+        alibi_slopes=None):
     """Writes dq, dk, dv in place (any row/head stride) and returns softmax_d = rowsum(dO*O).
-    Call site: flash_attn/flash_attn_interface.py:31-33."""
+    Call site: flash_attn/flash_attn_interface.py:31-33.  `gen` may be the PhiloxState of the forward (fwd_ex)."""
     return _bwd_impl(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seqlens_k, max_seqlen_q,
-                     max_seqlen_k, p_dropout, softmax_scale, zero_tensors, is_causal, gen)
+                     max_seqlen_k, p_dropout, softmax_scale, zero_tensors, is_causal, gen, seqused_q=seqused_q,
+                     seqused_k=seqused_k, alibi_slopes=alibi_slopes)
 
 
 def _check_qkv_packed(qkv, blockmask):
@@ -345,6 +445,13 @@ def _check_qkv_packed(qkv, blockmask):
 def fwd_block(qkv, cu_seqlens, blockmask, p_dropout, max_s, softmax_scale, is_causal, return_softmax, gen=None):
     """-> [context, softmax_lse (, S_dmask)].  Call site: flash_attn/flash_blocksparse_attn_interface.py:45-47.
     `blockmask` is the converted (ncol, nrow) int32 mask of convert_blockmask."""
+    _check_qkv_packed(qkv, blockmask)
+    return _fwd_impl(qkv[:, 0], qkv[:, 1], qkv[:, 2], cu_seqlens, cu_seqlens, max_s, max_s, p_dropout,
+                     softmax_scale, False, is_causal, return_softmax, gen, blockmask=blockmask)[0]
+
+
+def fwd_block_ex(qkv, cu_seqlens, blockmask, p_dropout, max_s, softmax_scale, is_causal, return_softmax, gen=None):
+    """fwd_block -> ([context, softmax_lse (, S_dmask)], PhiloxState or None), see fwd_ex."""
     _check_qkv_packed(qkv, blockmask)
     return _fwd_impl(qkv[:, 0], qkv[:, 1], qkv[:, 2], cu_seqlens, cu_seqlens, max_s, max_s, p_dropout,
                      softmax_scale, False, is_causal, return_softmax, gen, blockmask=blockmask)
@@ -372,42 +479,53 @@ def gather_rows(src2d, indices):
     _check(indices.dtype == torch.int64 and indices.is_contiguous(), "indices must be contiguous int64")
     out = torch.empty((indices.numel(), src2d.shape[1]), dtype=src2d.dtype, device=src2d.device)
     row_bytes = src2d.shape[1] * src2d.element_size()
-    with torch.cuda.device(src2d.device):
-        rc = _lib.fa_gather_rows(_ptr(out), _ptr(src2d), _ptr(indices), indices.numel(), row_bytes,
-                                 torch.cuda.current_stream().cuda_stream)
+    with _DeviceGuard(src2d.device) as guard:
+        rc = _lib.fa_gather_rows(_ptr(out), _ptr(src2d), _ptr(indices), indices.numel(), row_bytes, guard.raw_stream())
     _raise_if_failed(rc, "fa_gather_rows")
     return out
 
 
-def scatter_rows(src2d, indices, first_axis_dim):
-    """out = zeros(first_axis_dim, w); out[indices[i]] = src2d[i]."""
+def scatter_rows(src2d, indices, first_axis_dim, out=None):
+    """out = zeros(first_axis_dim, w) (or the given tensor, left untouched elsewhere); out[indices[i]] = src2d[i]."""
     _check(src2d.is_cuda and indices.is_cuda and src2d.dim() == 2 and src2d.is_contiguous(), "bad scatter input")
     _check(indices.dtype == torch.int64 and indices.is_contiguous(), "indices must be contiguous int64")
-    out = torch.zeros((first_axis_dim, src2d.shape[1]), dtype=src2d.dtype, device=src2d.device)
+    if out is None:
+        out = torch.zeros((first_axis_dim, src2d.shape[1]), dtype=src2d.dtype, device=src2d.device)
     row_bytes = src2d.shape[1] * src2d.element_size()
-    with torch.cuda.device(src2d.device):
-        rc = _lib.fa_scatter_rows(_ptr(out), _ptr(src2d), _ptr(indices), indices.numel(), row_bytes,
-                                  torch.cuda.current_stream().cuda_stream)
+    with _DeviceGuard(src2d.device) as guard:
+        rc = _lib.fa_scatter_rows(_ptr(out), _ptr(src2d), _ptr(indices), indices.numel(), row_bytes, guard.raw_stream())
     _raise_if_failed(rc, "fa_scatter_rows")
     return out
 
 
-def merge_partials(o_acc, lse_acc, lse_out, o_blk, lse_blk, batch, seqlen, first):
-    """Ring / split-KV merge (fa_merge_partials): o_acc fp32 (batch*seqlen, h, d) updated in place, lse_out written.
-    lse tensors are (batch, h, stride) fp32; o_blk is the 16-bit block output."""
+def merge_partials(o_acc, lse_acc, o_blk, lse_blk, batch, seqlen, first, batch_rows=None):
+    """Ring / split-KV merge (fa_merge_partials), in place: o_acc fp32 and o_blk 16 bit are (rows, h, d) tensors whose
+    row of (batch entry i, position t) is i * batch_rows + t (default batch_rows = seqlen); lse_acc / lse_blk are
+    (batch, h, >= seqlen) fp32 views whose last dimension is contiguous and whose (batch, h) dims are packed."""
+    batch_rows = seqlen if batch_rows is None else batch_rows
     _check(o_acc.is_cuda and o_acc.dtype == torch.float32 and o_acc.is_contiguous(), "o_acc must be contiguous fp32 CUDA")
-    _check(o_blk.dtype in (torch.float16, torch.bfloat16) and o_blk.is_contiguous() and o_blk.shape == o_acc.shape,
-           "o_blk must be contiguous fp16/bf16 with the shape of o_acc")
-    for t in (lse_acc, lse_out, lse_blk):
-        _check(t.dtype == torch.float32 and t.is_contiguous() and t.dim() == 3, "lse tensors must be contiguous (b, h, s) fp32")
-    _check(lse_acc.shape == lse_out.shape and lse_acc.data_ptr() != lse_out.data_ptr(), "lse_out must be a distinct buffer")
-    rows, h, d = o_acc.shape
-    _check(rows == batch * seqlen, "o_acc rows != batch * seqlen")
-    with torch.cuda.device(o_acc.device):
-        rc = _lib.fa_merge_partials(_ptr(o_acc), _ptr(lse_acc), _ptr(lse_out), _ptr(o_blk), _ptr(lse_blk), batch, h, d, seqlen,
-                                    lse_acc.shape[2], lse_blk.shape[2], 1 if o_blk.dtype == torch.bfloat16 else 0,
-                                    1 if first else 0, torch.cuda.current_stream().cuda_stream)
+    _check(o_blk.dtype in (torch.float16, torch.bfloat16) and o_blk.is_contiguous() and o_blk.shape[1:] == o_acc.shape[1:],
+           "o_blk must be contiguous fp16/bf16 with the row shape of o_acc")
+    for t in (lse_acc, lse_blk):
+        _check(t.dtype == torch.float32 and t.dim() == 3 and t.stride(2) == 1 and t.stride(0) == t.shape[1] * t.stride(1),
+               "lse tensors must be (b, h, s) fp32 with a contiguous last dim and packed (b, h)")
+    _, h, d = o_acc.shape
+    need = (batch - 1) * batch_rows + seqlen
+    _check(o_acc.shape[0] >= need and o_blk.shape[0] >= need, "o_acc / o_blk have too few rows")
+    with _DeviceGuard(o_acc.device) as guard:
+        rc = _lib.fa_merge_partials(_ptr(o_acc), _ptr(lse_acc), _ptr(o_blk), _ptr(lse_blk), batch, h, d, seqlen, batch_rows,
+                                    lse_acc.stride(1), lse_blk.stride(1), 1 if o_blk.dtype == torch.bfloat16 else 0,
+                                    1 if first else 0, guard.raw_stream())
     _raise_if_failed(rc, "fa_merge_partials")
+
+
+def accumulate_f32(dst, src, n_batches, run_elems, dst_batch_stride, src_batch_stride):
+    """dst (fp32) += src (16 bit) over n_batches runs of run_elems contiguous elements (fa_accumulate_f32)."""
+    _check(dst.is_cuda and dst.dtype == torch.float32 and src.dtype in (torch.float16, torch.bfloat16), "bad dtypes")
+    with _DeviceGuard(dst.device) as guard:
+        rc = _lib.fa_accumulate_f32(_ptr(dst), _ptr(src), n_batches, run_elems, dst_batch_stride, src_batch_stride,
+                                    1 if src.dtype == torch.bfloat16 else 0, guard.raw_stream())
+    _raise_if_failed(rc, "fa_accumulate_f32")
 
 
 def rotary_qk(qkv_in, qkv_out, cos, sin, seqlen, n_rot=2, conjugate=False):
@@ -423,10 +541,10 @@ def rotary_qk(qkv_in, qkv_out, cos, sin, seqlen, n_rot=2, conjugate=False):
     for t in (cos, sin):
         _check(t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and tuple(t.shape) == (seqlen, d // 2),
                "cos / sin must be contiguous fp32 (seqlen, d/2)")
-    with torch.cuda.device(qkv_in.device):
+    with _DeviceGuard(qkv_in.device) as guard:
         rc = _lib.fa_rotary_qk(_ptr(qkv_in), _ptr(qkv_out), _ptr(cos), _ptr(sin), rows, seqlen, n_parts, n_rot, h, d,
                                qkv_in.stride(0), qkv_out.stride(0), 1 if conjugate else 0,
-                               1 if qkv_in.dtype == torch.bfloat16 else 0, torch.cuda.current_stream().cuda_stream)
+                               1 if qkv_in.dtype == torch.bfloat16 else 0, guard.raw_stream())
     _raise_if_failed(rc, "fa_rotary_qk")
     return qkv_out
 

@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define FA_B200_ABI_VERSION 1
+#define FA_B200_ABI_VERSION 2
 
 enum {
   FA_OK = 0,
@@ -68,6 +68,16 @@ typedef struct fa_params {
                                flash_blocksparse_attn_interface.py:8-40; NULL for dense */
   void* workspace;          /* scratch, size >= fa_workspace_bytes() */
   uint64_t workspace_bytes;
+  /* --- optional device pointers (NULL = feature off) --------------------------------------- */
+  const int32_t* seqused_q; /* (b): rows of sequence i actually used, starting at cu_seqlens_q[i]; when given,
+                               cu_seqlens_q[i+1] is not read (sequences may leave gaps).  Lets one launch address
+                               sub-ranges of a packed batch (the K/V ring, flash_attn/ring_attention.py) */
+  const int32_t* seqused_k; /* (b): same for keys */
+  const float* alibi_slopes; /* (h) fp32: additive attention bias -slope[head] * |i - j| on the scaled scores
+                               (i, j = query / key index inside the sequence); gradient-free (README.md:57 roadmap) */
+  const uint64_t* philox_offset_ptr; /* device counter added (mod 2^32) to the low word of philox_offset when the
+                               kernel runs: a captured CUDA graph draws a fresh dropout mask per replay, like the
+                               reference's PhiloxCudaState (csrc/flash_attn/src/fmha.h:39, fmha_fprop_kernel_1xN.h:697) */
 
   /* --- strides, in elements (last dim must be contiguous) --------------------------------- */
   int64_t q_row_stride, q_head_stride;
@@ -92,12 +102,21 @@ typedef struct fa_params {
   int32_t is_causal;        /* top-left aligned: key j visible to query i iff j <= i */
   int32_t is_bf16;          /* 0 = fp16, 1 = bf16 */
   int32_t impl;             /* FA_IMPL_* */
-  int32_t reserved0;
+  uint32_t flags;           /* FA_FLAG_* */
   uint64_t philox_seed;     /* dropout RNG stream (position keyed: identical in fwd, bwd and s_dmask) */
   uint64_t philox_offset;
 } fa_params;
 
 enum { FA_OP_FWD = 0, FA_OP_BWD = 1, FA_OP_FWD_BLOCK = 2, FA_OP_BWD_BLOCK = 3 };
+
+/* fa_params.flags */
+enum {
+  /* backward: the caller guarantees that the workspace bytes named by fa_workspace_zero_range() are zero on entry
+   * (e.g. a buffer kept between calls on the same stream).  Every backward leaves that range zero again when it
+   * completes, so a persistent workspace needs to be cleared exactly once; without the flag the library clears it
+   * itself (one cudaMemsetAsync per call). */
+  FA_FLAG_WS_ZEROED = 1u
+};
 
 int fa_abi_version(void);
 uint64_t fa_sizeof_params(void);   /* sizeof(fa_params): lets a foreign-language binding verify its struct mirror */
@@ -111,8 +130,15 @@ uint64_t fa_launch_count(void);
 void fa_timing_enable(int on);
 int fa_timing_collect(double* fwd_ms, uint64_t* fwd_launches, double* bwd_ms, uint64_t* bwd_launches);
 
-/* bytes of scratch `op` needs for these sizes (0 if none). Pure host arithmetic. */
+/* bytes of scratch `op` needs for these sizes (0 if none). Pure host arithmetic.  The backward's scratch is
+ * O(total_q * h * d): statistics and the fp32 dQ accumulator are indexed by packed row, not by batch x max_seqlen. */
 uint64_t fa_workspace_bytes(const fa_params* p, int op);
+/* the part of the workspace that must be zero on entry when FA_FLAG_WS_ZEROED is set: bytes [*begin, *begin + return
+ * value) (return value 0: the op has no such region).  The rest of the workspace needs no initialisation. */
+uint64_t fa_workspace_zero_range(const fa_params* p, int op, uint64_t* begin);
+/* Graph-capturable dropout: out[0] = state[0]; state[0] += increment -- one tiny kernel on `stream`.  A captured
+ * forward passes `out` as philox_offset_ptr (and saves it for its backward); every replay then draws a new mask. */
+int fa_philox_advance(uint64_t* state, uint64_t* out, uint64_t increment, void* stream);
 /* how far the caller must advance its Philox offset after a call with dropout (fmha_api.cpp:228-234). */
 uint64_t fa_philox_increment(const fa_params* p);
 
@@ -131,14 +157,19 @@ int fa_scatter_rows(void* dst, const void* src, const int64_t* indices, int64_t 
                     void* stream);
 
 /* Merge of two partial attention results over the same queries (K/V split across ring steps / GPUs): the reference's
- * inter-K-block rule (csrc/flash_attn/src/fmha_fprop_kernel_1xN.h:606-650) applied to whole blocks.
- *   lse_out = log(exp(lse_acc) + exp(lse_blk));  o_acc = o_acc * exp(lse_acc - lse_out) + o_blk * exp(lse_blk - lse_out)
- * o_acc: fp32 (b * seqlen, h, d) contiguous, updated in place; o_blk: 16-bit (b * seqlen, h, d) contiguous;
- * lse_acc / lse_out: (b, h, lse_acc_stride) fp32, distinct buffers; lse_blk: (b, h, lse_blk_stride) fp32.
- * first != 0: initialise (o_acc = o_blk, lse_out = lse_blk; lse_acc is not read). */
-int fa_merge_partials(float* o_acc, const float* lse_acc, float* lse_out, const void* o_blk, const float* lse_blk, int32_t b,
-                      int32_t h, int32_t d, int32_t seqlen, int32_t lse_acc_stride, int32_t lse_blk_stride, int32_t is_bf16,
+ * inter-K-block rule (csrc/flash_attn/src/fmha_fprop_kernel_1xN.h:606-650) applied to whole blocks, in place:
+ *   lse' = log(exp(lse_acc) + exp(lse_blk));  o_acc = o_acc * exp(lse_acc - lse') + o_blk * exp(lse_blk - lse');  lse_acc = lse'
+ * o_acc fp32 and o_blk 16 bit: (rows, h, d) contiguous, the rows of batch entry i being i * batch_rows + t, t < seqlen
+ * (batch_rows > seqlen addresses one part of every sequence); lse_acc (b, h, lse_acc_stride), lse_blk (b, h, lse_blk_stride)
+ * fp32.  first != 0: initialise (o_acc = o_blk, lse_acc = lse_blk). */
+int fa_merge_partials(float* o_acc, float* lse_acc, const void* o_blk, const float* lse_blk, int32_t b, int32_t h, int32_t d,
+                      int32_t seqlen, int64_t batch_rows, int32_t lse_acc_stride, int32_t lse_blk_stride, int32_t is_bf16,
                       int32_t first, void* stream);
+
+/* dst (fp32) += src (fp16 / bf16) over n_batches runs of run_elems contiguous elements (multiples of 8; strides in
+ * elements): how the ring backward adds a step's dQ / dK / dV block into its fp32 accumulators. */
+int fa_accumulate_f32(float* dst, const void* src, int64_t n_batches, int64_t run_elems, int64_t dst_batch_stride,
+                      int64_t src_batch_stride, int32_t is_bf16, void* stream);
 
 /* Rotary position embedding of the first n_rot parts (q, k) of a packed (n_rows, n_parts, h, d) 16-bit tensor in one
  * pass -- replaces the pure-PyTorch apply_rotary_pos_emb + torch.stack the reference runs before attention in FlashMHA

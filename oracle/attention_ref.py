@@ -38,8 +38,17 @@ def causal_mask_topleft(seqlen_q, seqlen_k, device):
     return j > i
 
 
+def alibi_bias(alibi_slopes, seqlen_q, seqlen_k, device):
+    """EXTENSION (not in the reference's test oracle; its README.md:57 roadmap names "attention bias (e.g. ALiBi)"):
+    (h, sq, sk) additive bias -slope[h] * |i - j| on the scaled scores, i / j = query / key index inside the sequence
+    (top-left aligned like the causal mask above)."""
+    i = torch.arange(seqlen_q, device=device, dtype=torch.float32)[:, None]
+    j = torch.arange(seqlen_k, device=device, dtype=torch.float32)[None, :]
+    return -alibi_slopes.float().to(device)[:, None, None] * (i - j).abs()[None]
+
+
 def attention_ref(q, k, v, query_padding_mask=None, key_padding_mask=None, dropout_p=0.0,
-                  dropout_mask=None, causal=False, upcast=True, reorder_ops=False):
+                  dropout_mask=None, causal=False, upcast=True, reorder_ops=False, alibi_slopes=None):
     """Standard attention.  Restates tests/test_flash_attn.py:115-159.
 
     q: (b, sq, h, d); k, v: (b, sk, h, d); masks are bool (True = valid token);
@@ -58,6 +67,8 @@ def attention_ref(q, k, v, query_padding_mask=None, key_padding_mask=None, dropo
         scores = torch.einsum('bthd,bshd->bhts', q, k / rsqrt_d)        # :143
     else:
         scores = torch.einsum('bthd,bshd->bhts', q / rsqrt_d, k)        # :141
+    if alibi_slopes is not None:                                         # extension, see alibi_bias
+        scores = scores + alibi_bias(alibi_slopes, sq, sk, q.device)[None].to(scores.dtype)
     if key_padding_mask is not None:
         scores = scores.masked_fill(~_expand_key_mask(key_padding_mask), float('-inf'))   # :145
     if causal:
@@ -111,13 +122,15 @@ def expand_blockmask(blockmask, seqlen):
     return m[:seqlen, :seqlen]
 
 
-def attention_blocksparse_ref(qkv, blockmask, attn_mask, dropout_p, dropout_mask):
-    """Blocksparse attention oracle.  Restates tests/test_flash_attn.py:189-215.
+def attention_blocksparse_ref(qkv, blockmask, attn_mask, dropout_p, dropout_mask, upcast=True):
+    """Blocksparse attention oracle.  Restates tests/test_flash_attn.py:189-215 (upcast=False, an extension, runs the
+    same math in the input precision: the "PyTorch baseline" of the 2x rule, which the reference only has for the dense
+    oracle).
     qkv: (b, s, 3, h, d); blockmask (s/16, s/256); attn_mask (b, s) bool.
     Rows whose every block is masked produce NaN in the reference math (softmax of all -inf);
     here they are defined as zero output / zero attention, which is what the kernel emits
     (fully-masked-row rule)."""
-    q, k, v = qkv.float().unbind(dim=2)
+    q, k, v = (qkv.float() if upcast else qkv).unbind(dim=2)
     d, seqlen = qkv.shape[-1], qkv.shape[1]
     scores = torch.einsum('bthd,bshd->bhts', q / math.sqrt(d), k)
     scores = scores.masked_fill(~_expand_key_mask(attn_mask), float('-inf'))

@@ -104,3 +104,18 @@ def expected_dropout_mask(seed, offset, batch, heads, seqlen_q, seqlen_k, p_drop
                     keep = flash_attn_cuda.dropout_keep8_host(seed, offset, b * heads + h, i, g, p_dropout)
                     m[b, h, i, g * 8:(g + 1) * 8] = torch.tensor(keep)
     return m[..., :seqlen_k]
+
+
+class simt_kernels:
+    """Context manager: route the calls inside through the library's CUDA-core cross-check kernels (fa_params.impl =
+    FA_IMPL_SIMT).  Test-only: the product shim has no switch for this, the tests patch its module attribute."""
+
+    def __enter__(self):
+        import flash_attn_cuda
+        self.mod, self.old = flash_attn_cuda, flash_attn_cuda._impl
+        flash_attn_cuda._impl = flash_attn_cuda.FA_IMPL_SIMT
+        return self
+
+    def __exit__(self, *exc):
+        self.mod._impl = self.old
+        return False

@@ -86,17 +86,21 @@ def main():
         dmask = (torch.rand(b, h, sq, sk, generator=g) >= p) if p > 0 else torch.ones(b, h, sq, sk, dtype=torch.bool)
         qf, kf, vf = [x.clone().requires_grad_() for x in (q, k, v)]
         out_ref, attn_ref = t["attention_ref"](qf, kf, vf, qmask, kmask, p, dmask, causal=causal)
-        out_pt, attn_pt = t["attention_ref"](q, k, v, qmask, kmask, p, dmask, causal=causal, upcast=False,
+        qp, kp, vp = [x.clone().requires_grad_() for x in (q, k, v)]
+        out_pt, attn_pt = t["attention_ref"](qp, kp, vp, qmask, kmask, p, dmask, causal=causal, upcast=False,
                                              reorder_ops=True)
         dout = torch.randn(out_ref.shape, generator=g).to(dtype)
         dq, dk, dv = torch.autograd.grad(out_ref, (qf, kf, vf), dout)
+        # the 16-bit PyTorch path's own gradient error: the denominator of the reference's 2x rule (:407-418)
+        grads_pt = torch.autograd.grad(out_pt, (qp, kp, vp), dout)
+        grad_pt_maxerr = [(a.float() - r.float()).abs().max().item() for a, r in zip(grads_pt, (dq, dk, dv))]
         frac = t["get_dropout_fraction"](dmask.clone(), qmask, kmask, causal=causal).item()
         cases.append(dict(b=b, sq=sq, sk=sk, h=h, d=d, causal=causal, p=p, dtype=str(dtype), kind=kind,
                           q=q, k=k, v=v, qmask=qmask, kmask=kmask, dmask=pack_bool(dmask), dout=dout,
                           out_ref=out_ref.detach(), attn_ref=small_or_none(attn_ref.detach()),
                           out_pt_maxerr=(out_pt.float() - out_ref.detach().float()).abs().max().item(),
                           attn_pt_maxerr=(attn_pt.float() - attn_ref.detach().float()).abs().max().item(),
-                          dq=dq, dk=dk, dv=dv, dropout_fraction=frac))
+                          dq=dq, dk=dk, dv=dv, grad_pt_maxerr=grad_pt_maxerr, dropout_fraction=frac))
     torch.save(cases, os.path.join(OUT, "attention_ref_cases.pt"))
 
     # blocksparse oracle + blockmask conversion
@@ -108,7 +112,8 @@ def main():
         amask = t["generate_random_padding_mask"](s, b, "cpu", mode="random")
         dmask = (torch.rand(b, h, s, s, generator=g) >= p) if p > 0 else torch.ones(b, h, s, s, dtype=torch.bool)
         out, attn = t["attention_blocksparse_ref"](qkv, blockmask, amask, p, dmask)
-        bcases.append(dict(b=b, s=s, h=h, d=d, p=p, qkv=qkv, blockmask=blockmask, amask=amask, dmask=pack_bool(dmask),
+        out32, _ = t["attention_blocksparse_ref"](qkv.float(), blockmask, amask, p, dmask)   # same math, fp32 result
+        bcases.append(dict(out32=out32, b=b, s=s, h=h, d=d, p=p, qkv=qkv, blockmask=blockmask, amask=amask, dmask=pack_bool(dmask),
                            out=out, attn=small_or_none(attn, 300_000), converted=bs["convert_blockmask"](blockmask.clone(), False)))
     conv = []
     for (nrow, ncol, sp) in [(8, 1, 0.5), (16, 2, 0.3), (64, 4, 0.3), (128, 8, 0.7), (33, 5, 0.2), (16, 3, 1.0), (16, 3, 0.0)]:

@@ -56,7 +56,7 @@ def run_case(idx):
     dtype = torch.float16 if dt == "fp16" else torch.bfloat16
     dev = "cuda"
     torch.manual_seed(idx)
-    flash_attn_cuda.set_impl(impl)
+    flash_attn_cuda._impl = impl
     q = torch.randn(b, sq, h, d, device=dev, dtype=dtype)
     k = torch.randn(b, sk, h, d, device=dev, dtype=dtype)
     v = torch.randn(b, sk, h, d, device=dev, dtype=dtype)

@@ -15,12 +15,10 @@ from oracle import attention_ref as orc
 
 pytestmark = pytest.mark.gpu
 
-FULL = os.environ.get("FA_FULL_GRID", "0") == "1"
+# the reference's full grid (tests/test_flash_attn.py:332-345, 421-434, 514-527, 610-623) runs by default
 DTYPES = [torch.float16, torch.bfloat16]
 SEQLENS = [97, 128, 200, 256, 257, 384, 512, 768, 1024, 1025, 2048]
-SEQLENS_SMALL = SEQLENS if FULL else [97, 128, 257, 512, 1025, 2048]
 HEADDIMS = [32, 56, 64, 80, 96, 128]
-HEADDIMS_SMALL = HEADDIMS if FULL else [32, 64, 80, 128]
 BATCH, NHEADS = 32, 4
 
 
@@ -93,8 +91,8 @@ def test_flash_attn_unpadded_qkvpacked(seqlen, d, dropout_p, causal, dtype):
 
 @pytest.mark.parametrize("dtype", DTYPES)
 @pytest.mark.parametrize("causal", [False, True])
-@pytest.mark.parametrize("d", HEADDIMS_SMALL)
-@pytest.mark.parametrize("seqlen", SEQLENS_SMALL)
+@pytest.mark.parametrize("d", HEADDIMS)
+@pytest.mark.parametrize("seqlen", SEQLENS)
 @pytest.mark.parametrize("dropout_p", [0.0, 0.17])
 def test_flash_attn_unpadded_kvpacked(seqlen, d, dropout_p, causal, dtype):
     """tests/test_flash_attn.py:421-511: independent q / k padding masks => seqlen_q != seqlen_k."""
@@ -122,8 +120,8 @@ def test_flash_attn_unpadded_kvpacked(seqlen, d, dropout_p, causal, dtype):
 
 @pytest.mark.parametrize("dtype", DTYPES)
 @pytest.mark.parametrize("causal", [False, True])
-@pytest.mark.parametrize("d", HEADDIMS_SMALL)
-@pytest.mark.parametrize("seqlen", SEQLENS_SMALL)
+@pytest.mark.parametrize("d", HEADDIMS)
+@pytest.mark.parametrize("seqlen", SEQLENS)
 @pytest.mark.parametrize("dropout_p", [0.0, 0.17])
 def test_flash_attn_unpadded(seqlen, d, dropout_p, causal, dtype):
     """tests/test_flash_attn.py:514-607"""
@@ -158,7 +156,7 @@ def test_flash_attn_unpadded(seqlen, d, dropout_p, causal, dtype):
 @pytest.mark.parametrize("dtype", DTYPES)
 @pytest.mark.parametrize("causal", [False, True])
 @pytest.mark.parametrize("d", [128, 64, 32, 16])
-@pytest.mark.parametrize("seqlen", [97, 257, 1025, 2048] if not FULL else SEQLENS)
+@pytest.mark.parametrize("seqlen", SEQLENS)
 @pytest.mark.parametrize("dropout_p", [0.0, 0.17])
 def test_flash_attn_race_condition(seqlen, d, dropout_p, causal, dtype):
     """tests/test_flash_attn.py:610-671: bitwise run-to-run determinism of O and S_dmask (the reference's asserts)
@@ -181,7 +179,7 @@ def test_flash_attn_race_condition(seqlen, d, dropout_p, causal, dtype):
         return (out, S) + tuple(grads)
 
     first = run()
-    for _ in range(4 if not FULL else 10):
+    for _ in range(10):
         again = run()
         for i, (a, b) in enumerate(zip(first, again)):
             if i == 2:   # dQ

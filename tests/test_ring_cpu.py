@@ -17,49 +17,81 @@ from oracle import attention_ref as orc
 
 
 class TorchBlockOps:
-    """fp32 block operators with the CUDA kernels' semantics (test infrastructure)."""
+    """fp32 block operators with the CUDA kernels' semantics (test infrastructure).  All tensors are (b*2c, h, d)
+    local rows; a plan (q_off, q_len, k_len, causal) addresses chunk ranges of every 2c-row batch element."""
 
     @staticmethod
-    def _scores(q, k, n, c, scale, causal):
-        h, d = q.shape[1:]
-        qq, kk = q.reshape(n, c, h, d).float(), k.reshape(n, c, h, d).float()
+    def _parts(b, c, plan, *ts):
+        q_off, q_len, k_len, _ = plan
+        h, d = ts[0].shape[1:]
+        out = []
+        for t, is_q in ts[1:]:
+            t4 = t.reshape(-1, h, d)
+            pad = b * 2 * c - t4.shape[0]               # tensors may start at row q_off*c
+            t4 = torch.cat([t4.new_zeros(pad, h, d), t4]).reshape(b, 2 * c, h, d).float()
+            out.append(t4[:, q_off * c:(q_off + q_len) * c] if is_q else t4[:, :k_len * c])
+        return out
+
+    @staticmethod
+    def _scores(qq, kk, scale, causal):
         s = torch.einsum('bthd,bshd->bhts', qq, kk) * scale
         if causal:
-            s = s.masked_fill(orc.causal_mask_topleft(c, c, q.device), float('-inf'))
+            s = s.masked_fill(orc.causal_mask_topleft(qq.shape[1], kk.shape[1], qq.device), float('-inf'))
         return s
 
-    def fwd(self, q, k, v, n, c, scale, causal):
-        h, d = q.shape[1:]
-        s = self._scores(q, k, n, c, scale, causal)
+    @staticmethod
+    def _place(x, b, c, off, dtype):
+        """(b, n, h, d) -> rows from off*c on of a (b*2c, h, d) tensor"""
+        h, d = x.shape[2:]
+        full = x.new_zeros(b, 2 * c, h, d)
+        full[:, off * c:off * c + x.shape[1]] = x
+        return full.reshape(b * 2 * c, h, d)[off * c:].to(dtype)
+
+    def fwd(self, q, k, v, b, c, plan, scale):
+        qq, kk, vv = self._parts(b, c, plan, q, (q, True), (k, False), (v, False))
+        s = self._scores(qq, kk, scale, plan[3])
         lse = torch.logsumexp(s, dim=-1)
-        p = torch.exp(s - lse[..., None])
-        o = torch.einsum('bhts,bshd->bthd', p, v.reshape(n, c, h, d).float())
-        return o.reshape(n * c, h, d).to(q.dtype), lse
+        o = torch.einsum('bhts,bshd->bthd', torch.exp(s - lse[..., None]), vv)
+        return self._place(o, b, c, plan[0], q.dtype), lse
 
-    def bwd(self, dout, q, k, v, out, lse, n, c, scale, causal):
-        h, d = q.shape[1:]
-        s = self._scores(q, k, n, c, scale, causal)
-        p = torch.exp(s - lse[..., None])                       # FINAL lse: probabilities of the whole row
-        g = dout.reshape(n, c, h, d).float()
-        D = (g * out.reshape(n, c, h, d).float()).sum(-1).permute(0, 2, 1)      # (n, h, c)
-        dp = torch.einsum('bthd,bshd->bhts', g, v.reshape(n, c, h, d).float())
+    def bwd(self, dout, q, k, v, out, lse, b, c, plan, scale):
+        q_off, q_len, k_len, causal = plan
+        qq, gg, oo, kk, vv = self._parts(b, c, plan, q, (q, True), (dout, True), (out, True), (k, False), (v, False))
+        lse_v = lse[:, :, q_off * c:(q_off + q_len) * c]
+        p = torch.exp(self._scores(qq, kk, scale, causal) - lse_v[..., None])   # FINAL lse: probabilities of the whole row
+        D = (gg * oo).sum(-1).permute(0, 2, 1)                                   # (b, h, t)
+        dp = torch.einsum('bthd,bshd->bhts', gg, vv)
         ds = p * (dp - D[..., None])
-        dq = torch.einsum('bhts,bshd->bthd', ds, k.reshape(n, c, h, d).float()) * scale
-        dk = torch.einsum('bhts,bthd->bshd', ds, q.reshape(n, c, h, d).float()) * scale
-        dv = torch.einsum('bhts,bthd->bshd', p, g)
-        return tuple(t.reshape(n * c, h, d).to(q.dtype) for t in (dq, dk, dv))
+        dq = torch.einsum('bhts,bshd->bthd', ds, kk) * scale
+        dk = torch.einsum('bhts,bthd->bshd', ds, qq) * scale
+        dv = torch.einsum('bhts,bthd->bshd', p, gg)
+        junk = float('nan')                                                      # rows the kernels leave unwritten
+        dkf, dvf = [torch.full((b, 2 * c) + t.shape[2:], junk) for t in (dk, dv)]
+        dkf[:, :k_len * c], dvf[:, :k_len * c] = dk, dv
+        return (self._place(dq, b, c, q_off, q.dtype), dkf.reshape(b * 2 * c, *dk.shape[2:]).to(q.dtype),
+                dvf.reshape(b * 2 * c, *dv.shape[2:]).to(q.dtype))
 
-    def merge(self, o_acc, lse_acc, lse_out, o_blk, lse_blk, n, c, first):
+    def merge(self, o_acc, lse_acc, o_blk, lse_blk, b, c, plan, first):
+        q_off, q_len = plan[0], plan[1]
         h, d = o_acc.shape[1:]
+        oa = o_acc.reshape(b, 2 * c, h, d)[:, q_off * c:(q_off + q_len) * c]
+        ob = self._parts(b, c, plan, o_acc, (o_blk, True))[0]
+        la = lse_acc[:, :, q_off * c:(q_off + q_len) * c]
         if first:
-            o_acc.copy_(o_blk.float())
-            lse_out.copy_(lse_blk)
+            oa.copy_(ob)
+            la.copy_(lse_blk)
             return
-        new = torch.logaddexp(lse_acc, lse_blk)
-        wa = torch.exp(lse_acc - new).permute(0, 2, 1).reshape(n * c, h, 1)
-        wb = torch.exp(lse_blk - new).permute(0, 2, 1).reshape(n * c, h, 1)
-        o_acc.mul_(wa).add_(o_blk.float() * wb)
-        lse_out.copy_(new)
+        new = torch.logaddexp(la, lse_blk)
+        wa = torch.exp(la - new).permute(0, 2, 1)[..., None]
+        wb = torch.exp(lse_blk - new).permute(0, 2, 1)[..., None]
+        oa.copy_(oa * wa + ob * wb)
+        la.copy_(new)
+
+    def accumulate(self, dst, src, b, c, off, length):
+        h, d = dst.shape[1:]
+        pad = b * 2 * c - src.shape[0]
+        s4 = torch.cat([src.new_zeros(pad, h, d), src]).reshape(b, 2 * c, h, d).float()
+        dst.reshape(b, 2 * c, h, d)[:, off * c:(off + length) * c] += s4[:, off * c:(off + length) * c]
 
 
 def _free_port():
@@ -105,8 +137,8 @@ def test_ring_matches_full_causal_attention(world):
     assert max(errs) < 2e-5, errs
 
 
-def test_block_plan_covers_the_causal_triangle_exactly_once():
-    from flash_attn.ring_attention import _block_plan
+def test_step_plan_covers_the_causal_triangle_exactly_once():
+    from flash_attn.ring_attention import _step_plan
     for world in (1, 2, 3, 4, 8):
         seen = {}
         for rank in range(world):
@@ -114,13 +146,15 @@ def test_block_plan_covers_the_causal_triangle_exactly_once():
             for step in range(world):
                 src = (rank - step) % world
                 kchunk = {0: src, 1: 2 * world - 1 - src}
-                for qh, kh, causal in _block_plan(step, rank, world):
-                    pairs = [(0, 0), (1, 1)] if qh is None else [(qh, kh)]
-                    for a, bb in pairs:
+                q_off, q_len, k_len, causal = _step_plan(step, rank, world)
+                assert q_len * k_len == 2 or (step == 0 and causal)      # two c x c blocks of work per step and rank
+                for a in range(q_off, q_off + q_len):
+                    for bb in range(k_len):
                         key = (chunk[a], kchunk[bb])
+                        if causal and key[1] > key[0]:
+                            continue                                      # above the diagonal: masked inside the launch
                         assert key not in seen
                         seen[key] = causal
-                        assert causal == (key[0] == key[1])
+                        assert causal or key[1] < key[0]                 # full products lie strictly below the diagonal
         want = {(i, j) for i in range(2 * world) for j in range(2 * world) if j <= i}
         assert set(seen) == want
-        # balance: every rank computes the same number of c x c blocks

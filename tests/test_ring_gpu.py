@@ -1,6 +1,7 @@
 """GPU tests of the causal K/V ring (flash_attn/ring_attention.py) with the real kernels (CudaBlockOps):
-world_size 1 on any B200 (exercises the block schedule of step 0, fa_merge_partials and the block backward with the
-final lse), world_size 2 over NCCL when the box has two GPUs.  Acceptance: the reference's 2x rule against the fp32
+world_size 1 on any B200 (exercises the schedule of step 0, fa_merge_partials, fa_accumulate_f32 and the block backward
+with the final lse), world_size 2 / 4 / 8 over NCCL when the box has that many GPUs (every step kind, the overlapped
+K/V and dK/dV exchanges, the buffer recycling).  Acceptance: the reference's 2x rule against the fp32
 oracle over the WHOLE sequence (tests/test_flash_attn.py:407-418)."""
 import os
 import socket
@@ -58,12 +59,12 @@ def _worker(rank, world, port, b, S, h, d, dtype, ret):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world", [1, 2])
+@pytest.mark.parametrize("world", [1, 2, 4, 8])
 @pytest.mark.parametrize("d,dtype", [(128, torch.bfloat16), (64, torch.float16)])
 def test_ring_cuda_matches_full_causal_attention(world, d, dtype):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
-    b, S, h = 2, 256 * 2 * world, 3
+    b, S, h = 2, (256 if world <= 2 else 128) * 2 * world, 3
     ctx = mp.get_context("spawn")
     ret = ctx.SimpleQueue()
     mp.spawn(_worker, args=(world, _free_port(), b, S, h, d, dtype, ret), nprocs=world, join=True)
