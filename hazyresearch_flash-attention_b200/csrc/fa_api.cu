@@ -480,6 +480,58 @@ int fa_timing_collect(double* fwd_ms, uint64_t* fwd_launches, double* bwd_ms, ui
 
 int fa_fwd(const fa_params* p, void* stream) { return fa::run_fwd(p, stream, false); }
 int fa_bwd(const fa_params* p, void* stream) { return fa::run_bwd(p, stream, false); }
+// ---- fa_bwd_static_scratch: the backward with its scratch in a static device array (no allocation anywhere) ----
+// The array lives in this translation unit.  In HOST code its name is only a host-side stand-in for the symbol, not a
+// device address: the device address is obtained once per device, with that device current, by cudaGetSymbolAddress
+// (below) and that pointer is what the kernels receive as their workspace.
+static __device__ __align__(256) unsigned char g_static_scratch[FA_STATIC_SCRATCH_BYTES];
+
+namespace fa {
+namespace {
+// -> device address of g_static_scratch on the CURRENT device (cached per device ordinal), or nullptr + *err
+void* static_scratch_ptr(cudaError_t* err) {
+  static std::atomic<void*> cached[64];   // nullptr = not resolved yet; concurrent first calls just resolve twice
+  *err = cudaSuccess;
+  int dev = 0;
+  *err = cudaGetDevice(&dev);
+  if (*err != cudaSuccess) return nullptr;
+  void* ptr = (dev >= 0 && dev < 64) ? cached[dev].load(std::memory_order_acquire) : nullptr;
+  if (ptr == nullptr) {
+    *err = cudaGetSymbolAddress(&ptr, g_static_scratch);
+    if (*err != cudaSuccess) return nullptr;
+    if (dev >= 0 && dev < 64) cached[dev].store(ptr, std::memory_order_release);
+  }
+  return ptr;
+}
+}  // namespace
+}  // namespace fa
+
+int fa_bwd_static_scratch(const fa_params* p, void* stream) {
+  fa::g_last_error[0] = 0;
+  if (p == nullptr) return fa::fail(FA_ERR_INVALID_ARGUMENT, "params is NULL");
+  if (p->impl == FA_IMPL_SIMT)
+    return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_bwd_static_scratch runs the tcgen05 kernels only (impl must not be FA_IMPL_SIMT)");
+  int rc = fa::check_device();
+  if (rc != FA_OK) return rc;
+  fa_params q = *p;
+  q.workspace = nullptr;
+  q.workspace_bytes = 0;
+  const uint64_t need = fa_workspace_bytes(&q, FA_OP_BWD);
+  if (need > FA_STATIC_SCRATCH_BYTES)
+    return fa::fail(FA_ERR_WORKSPACE, "fa_bwd_static_scratch: these sizes need %llu bytes of scratch, the static array holds %llu "
+                    "(FA_STATIC_SCRATCH_BYTES); use fa_bwd with a caller-owned workspace",
+                    (unsigned long long)need, (unsigned long long)FA_STATIC_SCRATCH_BYTES);
+  cudaError_t e;
+  void* ptr = fa::static_scratch_ptr(&e);
+  if (ptr == nullptr) return fa::cuda_fail(e, "cudaGetSymbolAddress(g_static_scratch)");
+  q.workspace = ptr;
+  q.workspace_bytes = FA_STATIC_SCRATCH_BYTES;
+  // the array keeps the previous call's contents (possibly of other sizes): without this flag the backward clears, on
+  // `stream`, the range that has to start at zero (cudaMemsetAsync -- not an allocation)
+  q.flags &= ~static_cast<uint32_t>(FA_FLAG_WS_ZEROED);
+  return fa::run_bwd(&q, stream, false);
+}
+
 int fa_fwd_block(const fa_params* p, void* stream) { return fa::run_fwd(p, stream, true); }
 int fa_bwd_block(const fa_params* p, void* stream) { return fa::run_bwd(p, stream, true); }
 

@@ -59,7 +59,7 @@ def _load_library():
     lib.fa_workspace_bytes.argtypes = [ctypes.POINTER(FaParams), ctypes.c_int]
     lib.fa_philox_increment.restype = ctypes.c_uint64
     lib.fa_philox_increment.argtypes = [ctypes.POINTER(FaParams)]
-    for name in ("fa_fwd", "fa_bwd", "fa_fwd_block", "fa_bwd_block"):
+    for name in ("fa_fwd", "fa_bwd", "fa_fwd_block", "fa_bwd_block", "fa_bwd_static_scratch"):
         fn = getattr(lib, name)
         fn.restype = ctypes.c_int
         fn.argtypes = [ctypes.POINTER(FaParams), ctypes.c_void_p]

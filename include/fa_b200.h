@@ -147,6 +147,19 @@ int fa_bwd(const fa_params* p, void* stream);
 int fa_fwd_block(const fa_params* p, void* stream);
 int fa_bwd_block(const fa_params* p, void* stream);
 
+/* fa_bwd for callers that cannot allocate device memory (code under CUDA-graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same contract as fa_bwd, except that p->workspace / p->workspace_bytes are ignored: the scratch (fp32 dQ accumulator,
+ * tile counters, per-row statistics) is a file-scope static __device__ array of FA_STATIC_SCRATCH_BYTES inside the library
+ * (every GPU that loads the library holds that much until the process exits).  The call allocates nothing -- no
+ * cudaMalloc / cudaFree, no allocating library routine -- and fails with FA_ERR_WORKSPACE when
+ * fa_workspace_bytes(p, FA_OP_BWD) exceeds FA_STATIC_SCRATCH_BYTES (fa_last_error() states both numbers).
+ * All calls on a device share the one array, which keeps the previous call's contents: the part that must start at zero
+ * is cleared on `stream` by every call.  Calls that overlap on the GPU (different streams, or graphs replayed
+ * concurrently) RACE on it -- serialise them, or use fa_bwd with a caller-owned workspace. */
+#define FA_STATIC_SCRATCH_BYTES (32u << 20)
+int fa_bwd_static_scratch(const fa_params* p, void* stream);
+
 /* Varlen pack / unpack (bert_padding.py).  Rows are `row_bytes` long (multiple of 4 bytes).
  * gather : dst[i, :] = src[indices[i], :]             for i in [0, n_indices)
  * scatter: dst[indices[i], :] = src[i, :]             (dst rows not named by indices are left untouched)
