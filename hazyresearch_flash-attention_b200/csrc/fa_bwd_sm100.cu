@@ -6,8 +6,8 @@
 //     D = rowsum(dO o O)       dQ = scale * dS K          dK = scale * dS^T Q
 //
 // Two launches:  preprocess (D, -lse*log2e, per row)  ->  main.  The fp32 dQ accumulator is converted to 16 bit inside the
-// main kernel by whichever CTA adds the last contribution to a query tile (a counter per tile quarter); that CTA also
-// writes zeros back, so the accumulator is clean for the next call and needs neither a memset nor a postprocess pass.
+// main kernel by whichever CTA of a (batch, head) pair finishes last (one counter per pair, bumped once per CTA); that CTA
+// also writes zeros back, so the accumulator is clean for the next call and needs neither a memset nor a postprocess pass.
 // (The blocksparse variant, whose contributor count per tile depends on the mask, keeps the separate postprocess launch.)
 //
 // Main kernel: one CTA owns a block of 128 keys (K and V tiles stay in shared memory) and streams 128-row Q / dO tiles.
@@ -19,7 +19,7 @@
 // cp.reduce.async.bulk (one 8 KB bulk reduction per 16 head-dim columns); the postprocess kernel scales and converts it.
 // TMEM columns: S^T/P^T [0,128) | dP^T, then dQ [128,256) | dV [256,256+DPAD) | dK [384,384+DPAD).
 // Warps: 0-7 compute (warpgroup g handles query columns 64g..64g+63 of every tile), 8-11 dQ drain, 12 MMA issuer,
-// 13 TMA loader, 14 dQ finaliser (accumulator -> 16-bit dq for completed tiles), 15 zero-fill of rows beyond a sequence.
+// 13 TMA loader, 14 idle, 15 zero-fill of rows beyond a sequence.
 #include <cudaTypedefs.h>
 
 #include <atomic>
@@ -58,14 +58,20 @@ struct BwdSmem {
   static constexpr int kMaskOff = kStatOff + kQStages * 1024;    // dropout keep bits: 2 x [4 key words][128 queries] u32
   static constexpr int kListOff = kMaskOff + 2 * 2048;    // blocksparse: int16 list[512], uint8 flags[512]
   static constexpr int kBarOff = kListOff + kMaxSparseTiles * 3;
-  static constexpr int kNumBars = 21;                     // + k_fix, q_fix, do_fix
+  static constexpr int kNumBars = 27;                     // + k_fix, q_fix, do_fix, fin_full[3], fin_empty[3]
+  // dQ finalisation at the end of a (batch, head)'s last CTA: ring of kFinStages accumulator tiles over the (then dead)
+  // K / V / Q / dO / dS buffers, a 16 KB block of zeros in the dQ staging area
+  static constexpr int kFinStages = 3;
+  static constexpr int kAccTile = 128 * DPAD * 4;         // one fp32 accumulator tile
+  static constexpr int kZeroBytes = 16384;
   static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
-  static constexpr int kFinQueueOff = kTmemPtrOff + 16;   // dQ finaliser queue: tail, head, drains done, pad, entries[kFinQueue]
-  static constexpr int kFinQueue = 64;
-  static constexpr int kTotal = kFinQueueOff + 16 + kFinQueue * 4;
+  static constexpr int kTotal = kTmemPtrOff + 16;
   static constexpr int kDynamicBytes = kTotal + 1024;     // + alignment slack
 };
 static_assert(BwdSmem<128>::kDynamicBytes <= 232448, "shared memory budget");
+static_assert(BwdSmem<128>::kFinStages * BwdSmem<128>::kAccTile <= BwdSmem<128>::kDqOff &&
+              BwdSmem<64>::kFinStages * BwdSmem<64>::kAccTile <= BwdSmem<64>::kDqOff, "finalisation ring overlaps the zero block");
+static_assert(BwdSmem<128>::kZeroBytes <= 4 * BwdSmem<128>::kDqBufs * 2048, "zero block must fit the dQ staging area");
 
 struct BwdTensorMaps {
   CUtensorMap q, k, v, dout;
@@ -78,7 +84,7 @@ struct BwdWs {
   float* nl;         // (h, n_slots * 128): -lse*log2e, -inf for rows that must produce P = 0
   float* dsum;       // (h, n_slots * 128): D = rowsum(dO o O), 0 for invalid rows
   float* dq_accum;   // (h, n_slots, 4 row quarters, DPAD/4, 32, 4) fp32; all zero on entry and on exit
-  uint32_t* dq_count;   // (h, n_slots, 4): contributions received per tile quarter; all zero on entry and on exit
+  uint32_t* dq_count;   // (h, n_slots, 4): word 0 of a sequence's first slot counts its finished key-block CTAs; zero on entry and exit
   int n_slots;
 };
 __device__ __forceinline__ int tile_slot(int q_begin, int bidb, int m) { return (q_begin >> 7) + bidb + m; }
@@ -209,11 +215,11 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
   uint64_t* k_fix = bars + 18;
   uint64_t* q_fix = bars + 19;
   uint64_t* do_fix = bars + 20;
-  volatile uint32_t* fin_q = reinterpret_cast<volatile uint32_t*>(smem + L::kFinQueueOff);   // [0] tail [1] head [2] drains done
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + L::kTmemPtrOff);
   int16_t* tile_list = reinterpret_cast<int16_t*>(smem + L::kListOff);
   uint8_t* tile_flags = smem + L::kListOff + kMaxSparseTiles * 2;
   __shared__ int s_num_active;
+  __shared__ uint32_t s_bh_last;
 
   // Q tiles this CTA visits
   const int n_qt_total = (seq.seqlen_q + kBM - 1) / kBM;
@@ -257,7 +263,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
   const bool kv_partial = k_valid < kBN;
   const int q_valid_last = seq.seqlen_q - (n_qt_total - 1) * kBM;   // valid rows of the last query tile (1..128)
   const bool q_partial = n_iter > 0 && q_valid_last < kBM && tile_of(n_iter - 1) == n_qt_total - 1;   // then it is the last iteration
-  constexpr bool kFusedDq = !kSparse;                    // dQ finalised in-kernel (see the drain / finaliser warps)
+  constexpr bool kFusedDq = !kSparse;                    // dQ finalised in-kernel (see the end of the kernel)
   const int slot0 = tile_slot(seq.q_begin, bidb, 0);
 
   uint8_t* sK = smem + L::kKOff;
@@ -319,10 +325,8 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     mbar_init(dq_full, 1);
     mbar_init(dq_empty, 128);
     mbar_init(dkv_full, 1);
-    fin_q[0] = 0; fin_q[1] = 0; fin_q[2] = 0;
     fence_mbar_init();
   }
-  if (threadIdx.x >= 64 && threadIdx.x < 64 + L::kFinQueue) fin_q[4 + threadIdx.x - 64] = 0xFFFFFFFFu;   // empty slot
   if (warp == 0) {
     tmem_alloc(tmem_ptr_smem, 512);
     tmem_relinquish();
@@ -332,9 +336,9 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
   if (threadIdx.x == 0) FA_CTA_MARK(3, clock64());
-  // dQ tile (b, m) is complete when every key-block CTA that visits it has added its partial
+  // the dQ tiles of this (batch, head) are complete when every key-block CTA of the sequence (the ones that did not
+  // return above: n_blk < nkb_seq) has added its partials -- see the end of the kernel
   const int nkb_seq = (seq.seqlen_k + kBN - 1) / kBN;
-  auto dq_contributors = [&](int m) -> uint32_t { return static_cast<uint32_t>(kCausal ? min(m + 1, nkb_seq) : nkb_seq); };
   auto dq_row_ptr = [&](int row) -> uint16_t* {   // row within the sequence
     return row < seq.seqlen_q ? reinterpret_cast<uint16_t*>(p.dq) + (int64_t)(seq.q_begin + row) * p.dq_row_stride + (int64_t)bidh * p.dq_head_stride
                               : nullptr;
@@ -554,40 +558,6 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
         zero_rows(smem_u32(sDo), q_valid_last);
         if (lane == 0) mbar_arrive(do_full);
       }
-    } else {
-      // ===================================== dQ finaliser (warp 14) ============================
-      // Tile quarters whose last contribution came from this CTA (queued by the drain warps) are converted here, off
-      // the drain warps' critical path: accumulator (L2) -> dq, zeros written back.
-      if constexpr (kFusedDq) {
-        uint32_t head = 0;
-        uint64_t idle_since = 0;               // like mbar_wait: a protocol bug traps instead of hanging the GPU
-        while (true) {
-          const uint32_t done = fin_q[2];      // read before the tail: a drain warp queues before it reports done
-          const uint32_t tail = fin_q[0];
-          if (head == tail) {
-            if (done == 4) break;
-            __nanosleep(200);
-            const uint64_t now = global_timer_ns();
-            if (idle_since == 0) idle_since = now;
-            else if (now - idle_since > 4 * FA_WAIT_TIMEOUT_NS) { asm volatile("trap;\n"); }
-            continue;
-          }
-          idle_since = 0;
-          uint32_t e;
-          while ((e = fin_q[4 + head % L::kFinQueue]) == 0xFFFFFFFFu) __nanosleep(32);
-          __threadfence();                     // acquire side of the drain warp's counter update
-          const int m = static_cast<int>(e >> 2), q4 = static_cast<int>(e & 3u);
-          float* acc = ws.dq_accum + ((int64_t)bidh * ws.n_slots + slot0 + m) * (kBM * DPAD) + q4 * (32 * DPAD);
-          finalize_dq_quarter<DPAD, kBf16, 2>(acc, dq_row_ptr(m * kBM + q4 * 32 + lane), p.d, p.softmax_scale, lane);
-          __syncwarp();
-          if (lane == 0) {
-            fin_q[4 + head % L::kFinQueue] = 0xFFFFFFFFu;
-            __threadfence_block();
-            fin_q[1] = head + 1;
-          }
-          ++head;
-        }
-      }
     }
   } else if (warp >= 8) {
     // ===================================== dQ drain warps ======================================
@@ -602,36 +572,6 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     constexpr int kChunks = DPAD / 16;
     constexpr int kRing = kChunks < 8 ? kChunks : 8;
     uint32_t n_issued = 0;
-    // Completion protocol (kFusedDq): once the reductions of a tile have COMPLETED (bulk wait_group without .read), the
-    // warp bumps the tile quarter's counter; the warp that brings it to the number of contributing key blocks owns the
-    // finished sum.  Tile it-1 is signalled after tile it has been issued, so the wait never stalls the drain; the
-    // conversion goes to the finaliser warp's queue, except for the CTA's last tile, which this warp converts itself.
-    auto signal_tile = [&](int m_done, bool last_tile) {
-      uint32_t is_last = 0;
-      if (lane == 0) {
-        if (last_tile) bulk_wait_group<0>(); else bulk_wait_group<kChunks>();
-        __threadfence();
-        uint32_t* cnt = ws.dq_count + ((int64_t)bidh * ws.n_slots + slot0 + m_done) * 4 + wq;
-        const uint32_t old = atomicAdd(cnt, 1u);
-        if (old + 1 == dq_contributors(m_done)) {
-          is_last = 1;
-          __threadfence();
-          *cnt = 0;                           // clean for the next call
-        }
-      }
-      is_last = __shfl_sync(0xffffffffu, is_last, 0);
-      if (is_last) {
-        if (last_tile) {
-          float* acc = ws.dq_accum + ((int64_t)bidh * ws.n_slots + slot0 + m_done) * (kBM * DPAD) + wq * (32 * DPAD);
-          finalize_dq_quarter<DPAD, kBf16, 4>(acc, dq_row_ptr(m_done * kBM + wq * 32 + lane), p.d, p.softmax_scale, lane);
-        } else if (lane == 0) {
-          uint32_t* q32 = const_cast<uint32_t*>(fin_q);
-          const uint32_t idx = atomicAdd(q32, 1u);
-          while (idx - fin_q[1] >= static_cast<uint32_t>(L::kFinQueue)) __nanosleep(64);   // queue full: wait for the finaliser
-          fin_q[4 + idx % L::kFinQueue] = (static_cast<uint32_t>(m_done) << 2) | static_cast<uint32_t>(wq);
-        }
-      }
-    };
     for (int it = 0; it < n_iter; ++it) {
       const int m = tile_of(it);
       float* gdst = ws.dq_accum + ((int64_t)bidh * ws.n_slots + slot0 + m) * (kBM * DPAD) + wq * (32 * DPAD);
@@ -680,15 +620,30 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
         }
       }
       if (wq == 0) FA_TRACE(18);
-      if (kFusedDq && it > 0) signal_tile(tile_of(it - 1), false);
     }
     if (warp == 8 && lane == 0) FA_CTA_MARK(9, clock64());    // last chunk issued
     if constexpr (kFusedDq) {
-      if (n_iter > 0) signal_tile(tile_of(n_iter - 1), true);
+      // The CTA's contribution counts once its reductions have COMPLETED (wait_group without .read: the sums are in L2).
+      // The four drain warps meet on a named barrier and warp 8 bumps the (batch, head) counter right here, so that the
+      // completion wait, the fence and the atomic's round trip (2-3 us together) run under the dK / dV epilogue of the
+      // compute warps instead of after it; the verdict reaches the other warps through the CTA-wide barrier at the end.
+      if (lane == 0) bulk_wait_group<0>();
       __syncwarp();
-      if (lane == 0) {
-        __threadfence_block();
-        atomicAdd(const_cast<uint32_t*>(fin_q) + 2, 1u);   // this drain warp has queued everything it ever will
+      named_bar_sync(4, 128);
+      if (warp == 8 && lane == 0) {
+        uint32_t* cnt = ws.dq_count + ((int64_t)bidh * ws.n_slots + slot0) * 4;
+        __threadfence();
+        const uint32_t old = atomicAdd(cnt, 1u);
+        const bool last = old + 1 == static_cast<uint32_t>(nkb_seq);
+        if (last) {
+          *cnt = 0;                       // clean for the next call
+          for (int st = 0; st < L::kFinStages; ++st) {
+            mbar_init(&bars[21 + st], 1);                    // fin_full
+            mbar_init(&bars[24 + st], kBwdThreads / 32);     // fin_empty
+          }
+          fence_mbar_init();
+        }
+        s_bh_last = last ? 1 : 0;
       }
     } else {
       if (lane == 0) bulk_wait_group_read<0>();   // the staging buffers may go away; the reductions complete on their own
@@ -907,6 +862,80 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
   }
+  if constexpr (kFusedDq) {
+    // dQ finalisation.  ONE counter per (batch, head), bumped once per CTA by the drain warps (see there) after their bulk
+    // reductions have completed; s_bh_last is their verdict.  The CTA that brings it to the number of key blocks owns the
+    // finished sums of every query tile of this (batch, head): it converts them (fp32 accumulator in L2 -> x scale ->
+    // 16-bit dq) and writes zeros back, which leaves accumulator and counter clean for the next call -- no memset, no
+    // postprocess launch.  (Per-tile counters were measured first: a fence + atomic per tile and drain warp sits on the
+    // dQ -> drain -> dP chain and cost 50 % of the kernel, profiles/r02_dq_signal_ab.log.)
+    uint64_t* fin_full = bars + 21;
+    uint64_t* fin_empty = bars + 24;
+    if (s_bh_last != 0 && n_qt_total > 0) {
+      // Every buffer of the CTA is dead now.  The accumulator tiles come in through bulk copies (a 3-deep ring, completion
+      // on mbarriers), all 16 warps convert out of shared memory, and the zeros go back as bulk stores from a zeroed
+      // 16 KB block -- no register-latency-bound loads, the copy engine runs at the SM's full L2 bandwidth.
+      constexpr int kChunks = DPAD / 16;
+      uint8_t* fbuf = smem;
+      uint8_t* zbuf = smem + L::kDqOff;
+      for (int i = threadIdx.x; i < L::kZeroBytes / 16; i += kBwdThreads) st_shared_v4(smem_u32(zbuf) + i * 16, 0u, 0u, 0u, 0u);
+      fence_proxy_async();
+      __syncthreads();
+      float* acc0 = ws.dq_accum + ((int64_t)bidh * ws.n_slots + slot0) * (kBM * DPAD);
+      const bool producer = threadIdx.x == 0;
+      if (producer) {
+        __threadfence();            // acquire side of the counter: the other CTAs' completed reductions ...
+        fence_proxy_async_all();    // ... before this thread's bulk copies read them
+        for (int st = 0; st < L::kFinStages && st < n_qt_total; ++st) {
+          mbar_arrive_expect_tx(&fin_full[st], L::kAccTile);
+          bulk_load_1d(fbuf + st * L::kAccTile, acc0 + (int64_t)st * (kBM * DPAD), L::kAccTile, &fin_full[st]);
+        }
+      }
+      const int q4 = warp & 3;
+      const float sc = p.softmax_scale;
+      for (int m = 0; m < n_qt_total; ++m) {
+        const int st = m % L::kFinStages;
+        mbar_wait(&fin_full[st], (m / L::kFinStages) & 1);
+        uint16_t* dq_row = dq_row_ptr(m * kBM + q4 * 32 + lane);
+        const uint32_t qbase = smem_u32(fbuf) + st * L::kAccTile + q4 * (32 * DPAD * 4) + lane * 16;
+#pragma unroll
+        for (int k = warp >> 2; k < kChunks; k += 4) {   // quarter layout: [chunk (16 columns)][4 column groups][32 rows][4]
+          const float4 v0 = lds128(qbase + k * 2048), v1 = lds128(qbase + k * 2048 + 512);
+          const float4 v2 = lds128(qbase + k * 2048 + 1024), v3 = lds128(qbase + k * 2048 + 1536);
+          uint4 lo, hi;
+          lo.x = pack2<kBf16>(v0.x * sc, v0.y * sc);
+          lo.y = pack2<kBf16>(v0.z * sc, v0.w * sc);
+          lo.z = pack2<kBf16>(v1.x * sc, v1.y * sc);
+          lo.w = pack2<kBf16>(v1.z * sc, v1.w * sc);
+          hi.x = pack2<kBf16>(v2.x * sc, v2.y * sc);
+          hi.y = pack2<kBf16>(v2.z * sc, v2.w * sc);
+          hi.z = pack2<kBf16>(v3.x * sc, v3.y * sc);
+          hi.w = pack2<kBf16>(v3.z * sc, v3.w * sc);
+          const int col = k * 16;
+          if (dq_row != nullptr && col < p.d) *reinterpret_cast<uint4*>(dq_row + col) = lo;
+          if (dq_row != nullptr && col + 8 < p.d) *reinterpret_cast<uint4*>(dq_row + col + 8) = hi;
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&fin_empty[st]);
+        if (producer) {
+          // tile m has landed (fin_full observed): its zeros can go back right away
+          float* acc_m = acc0 + (int64_t)m * (kBM * DPAD);
+#pragma unroll
+          for (int z = 0; z < L::kAccTile / L::kZeroBytes; ++z)
+            bulk_store_1d(reinterpret_cast<uint8_t*>(acc_m) + z * L::kZeroBytes, zbuf, L::kZeroBytes);
+          bulk_commit_group();
+          // refill the stage tile m-1 used, one iteration late: by now every warp has long arrived on its barrier
+          if (m >= 1 && m - 1 + L::kFinStages < n_qt_total) {
+            const int sp = (m - 1) % L::kFinStages;
+            mbar_wait(&fin_empty[sp], ((m - 1) / L::kFinStages) & 1);
+            mbar_arrive_expect_tx(&fin_full[sp], L::kAccTile);
+            bulk_load_1d(fbuf + sp * L::kAccTile, acc0 + (int64_t)(m - 1 + L::kFinStages) * (kBM * DPAD), L::kAccTile, &fin_full[sp]);
+          }
+        }
+      }
+      if (producer) bulk_wait_group_read<0>();   // the zero block is read by stores still in flight
+    }
+  }
 #ifdef FA_BWD_TRACE
   if (threadIdx.x == 0) {
     FA_CTA_MARK(5, clock64());
@@ -1122,8 +1151,16 @@ cudaError_t launch_bwd_sm100(const fa_params& p, const BlockMaskView& bm, void* 
       *err_msg = "cuTensorMapEncodeTiled failed (q/k/v/dout must be 16-byte aligned with 16-byte-multiple strides)";
       return cudaErrorInvalidValue;
     }
+#ifdef FA_BWD_FEW_VARIANTS   // experiment builds (tools/build_variants.sh): only the headline instantiation, seconds to compile
+    if (p.d > 64 && p.is_bf16 && p.is_causal && !(p.p_dropout > 0.f) && bm.dense == nullptr && p.alibi_slopes == nullptr)
+      e = launch_bwd_variant<128, true, true, false, false, false>(maps, p, bm, ws, stream);
+    else if (p.d > 64 && p.is_bf16 && !p.is_causal && !(p.p_dropout > 0.f) && bm.dense == nullptr && p.alibi_slopes == nullptr)
+      e = launch_bwd_variant<128, true, false, false, false, false>(maps, p, bm, ws, stream);
+    else e = cudaErrorNotSupported;
+#else
     if (p.d <= 64) e = p.is_bf16 ? dispatch_bwd_flags<64, true>(maps, p, bm, ws, stream) : dispatch_bwd_flags<64, false>(maps, p, bm, ws, stream);
     else e = p.is_bf16 ? dispatch_bwd_flags<128, true>(maps, p, bm, ws, stream) : dispatch_bwd_flags<128, false>(maps, p, bm, ws, stream);
+#endif
     if (e != cudaSuccess) return e;
   }
   if (bm.dense != nullptr && n_qtiles > 0 && p.total_q > 0) {
