@@ -226,8 +226,10 @@ def ring_record(args, w, world, rank, local_rank, device, dist, steps, warmup):
             "workload": w["name"], "per_gpu_tflops": value / world,
             "frac_of_bf16_peak_per_gpu": value / world / peaks["burst"],
             "kv_block_bytes_per_hop": 2 * 2 * b * c * h * d * 2, "dkv_block_bytes_per_hop": 2 * 2 * b * c * h * d * 4,
-            "exchange": "K/V (bf16) and, in the backward, the fp32 dK/dV accumulator rotate rank->rank+1 with NCCL P2P; each "
-                        "transfer overlaps an attention kernel (K/V: the same step's, dK/dV: the next step's)",
+            "exchange": "K/V (bf16) and, in the backward, the fp32 dK/dV accumulator move rank->rank+1 as copy-engine pulls out of "
+                        "the predecessor's CUDA-IPC-mapped buffer over NVLink, ordered by flag kernels; each transfer overlaps an "
+                        "attention kernel (K/V: the same step's, dK/dV: the next step's)",
+            "transport": ring.default_transport or "peer (world > 1)",
             "parity_check_max_abs_err": errs, "gpu_launches_per_step": launches / steps,
             "l2": "per-GPU inputs exceed L2 at every N <= 8 (no flush needed)"}
 

@@ -3,6 +3,8 @@
 // (csrc/flash_attn/fmha_api.cpp:38-242, src/fmha_fprop_kernel_dispatch.cu:90-134) -- but torch-free, never
 // allocating, never synchronising, and reporting errors by return code instead of exit(1)
 // (src/fmha_utils.h:37-48).
+#include <cuda.h>
+
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -218,6 +220,30 @@ __global__ void __launch_bounds__(256) accumulate_f32_kernel(float* __restrict__
     d4[0] = a0;
     d4[1] = a1;
   }
+}
+
+// Cross-GPU signalling for the peer-memory ring (flash_attn/ring_attention.py): monotone 64-bit counters in memory that a
+// peer process has mapped through CUDA IPC.  The writer's stream has completed everything the value announces (stream
+// order), the system-scope fence publishes it; the waiter spins on its own stream until the counter has reached the value.
+__global__ void flag_write_kernel(uint64_t* flag, uint64_t value) {
+  __threadfence_system();
+  *reinterpret_cast<volatile uint64_t*>(flag) = value;
+  __threadfence_system();
+}
+__global__ void flag_wait_geq_kernel(const uint64_t* flag, uint64_t value, uint64_t timeout_ns) {
+  const volatile uint64_t* f = reinterpret_cast<const volatile uint64_t*>(flag);
+  uint64_t t0 = 0;
+  uint32_t spins = 0;
+  while (*f < value) {
+    __nanosleep(200);
+    if ((++spins & 1023u) == 0) {      // a lost peer must surface as a launch failure, never as a hung GPU
+      uint64_t now;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > timeout_ns) { asm volatile("trap;\n"); }
+    }
+  }
+  __threadfence_system();
 }
 
 __global__ void philox_advance_kernel(uint64_t* state, uint64_t* out, uint64_t increment) {
@@ -579,6 +605,93 @@ int fa_accumulate_f32(float* dst, const void* src, int64_t n_batches, int64_t ru
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fa::cuda_fail(e, "accumulate_f32 launch");
   return FA_OK;
+}
+
+int fa_flag_write(uint64_t* flag, uint64_t value, void* stream) {
+  fa::g_last_error[0] = 0;
+  if (flag == nullptr) return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_flag_write: NULL flag");
+  fa::flag_write_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(flag, value);
+  fa::count_launch();
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? FA_OK : fa::cuda_fail(e, "flag_write launch");
+}
+
+int fa_flag_wait_geq(const uint64_t* flag, uint64_t value, uint64_t timeout_ms, void* stream) {
+  fa::g_last_error[0] = 0;
+  if (flag == nullptr) return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_flag_wait_geq: NULL flag");
+  if (timeout_ms == 0) timeout_ms = 20000;
+  fa::flag_wait_geq_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(flag, value, timeout_ms * 1000000ull);
+  fa::count_launch();
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? FA_OK : fa::cuda_fail(e, "flag_wait_geq launch");
+}
+
+// CUDA IPC for the peer-memory ring.  The handle names the whole cudaMalloc allocation that contains `ptr` (a framework's
+// caching allocator hands out sub-ranges), so the offset of `ptr` inside it travels with the handle.
+int fa_ipc_export(const void* ptr, uint8_t handle[64], uint64_t* offset) {
+  fa::g_last_error[0] = 0;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  if (ptr == nullptr || handle == nullptr || offset == nullptr) return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_ipc_export: NULL pointer");
+  typedef CUresult (*GetRange)(CUdeviceptr*, size_t*, CUdeviceptr);
+  static GetRange get_range = [] {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &fn, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) fn = nullptr;
+    return reinterpret_cast<GetRange>(fn);
+  }();
+  if (get_range == nullptr) return fa::fail(FA_ERR_CUDA, "fa_ipc_export: cuMemGetAddressRange is not available");
+  CUdeviceptr base = 0;
+  size_t size = 0;
+  if (get_range(&base, &size, reinterpret_cast<CUdeviceptr>(ptr)) != CUDA_SUCCESS)
+    return fa::fail(FA_ERR_CUDA, "fa_ipc_export: cuMemGetAddressRange failed (not a device allocation?)");
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, reinterpret_cast<void*>(base));
+  if (e != cudaSuccess) return fa::cuda_fail(e, "cudaIpcGetMemHandle");
+  memcpy(handle, &h, 64);
+  *offset = reinterpret_cast<CUdeviceptr>(ptr) - base;
+  return FA_OK;
+}
+
+int fa_ipc_open(const uint8_t handle[64], void** base) {
+  fa::g_last_error[0] = 0;
+  if (handle == nullptr || base == nullptr) return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_ipc_open: NULL pointer");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, 64);
+  // opened with the CALLER's device current: the mapping belongs to this device's context and peer access to the
+  // exporting GPU is enabled along with it, so this device's kernels and copies can use the addresses directly
+  cudaError_t e = cudaIpcOpenMemHandle(base, h, cudaIpcMemLazyEnablePeerAccess);
+  return e == cudaSuccess ? FA_OK : fa::cuda_fail(e, "cudaIpcOpenMemHandle");
+}
+
+int fa_ipc_close(void* base) {
+  fa::g_last_error[0] = 0;
+  if (base == nullptr) return FA_OK;
+  cudaError_t e = cudaIpcCloseMemHandle(base);
+  return e == cudaSuccess ? FA_OK : fa::cuda_fail(e, "cudaIpcCloseMemHandle");
+}
+
+int fa_enable_peer_access(int32_t peer_device) {
+  fa::g_last_error[0] = 0;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fa::cuda_fail(e, "cudaGetDevice");
+  if (peer_device == dev) return FA_OK;
+  int can = 0;
+  e = cudaDeviceCanAccessPeer(&can, dev, peer_device);
+  if (e != cudaSuccess) return fa::cuda_fail(e, "cudaDeviceCanAccessPeer");
+  if (!can) return fa::fail(FA_ERR_UNSUPPORTED_DEVICE, "device %d cannot access device %d as a peer (no NVLink / P2P path)", dev, peer_device);
+  e = cudaDeviceEnablePeerAccess(peer_device, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); return FA_OK; }   // clear the sticky-less error state
+  return e == cudaSuccess ? FA_OK : fa::cuda_fail(e, "cudaDeviceEnablePeerAccess");
+}
+
+int fa_peer_copy(void* dst, const void* src, uint64_t bytes, void* stream) {
+  fa::g_last_error[0] = 0;
+  if (bytes == 0) return FA_OK;
+  if (dst == nullptr || src == nullptr) return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_peer_copy: NULL pointer");
+  // unified addressing: the driver sees that src lives on a peer device and uses a copy engine over NVLink
+  cudaError_t e = cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, static_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? FA_OK : fa::cuda_fail(e, "cudaMemcpyAsync (peer)");
 }
 
 int fa_gather_rows(void* dst, const void* src, const int64_t* indices, int64_t n_indices, int64_t row_bytes, void* stream) {

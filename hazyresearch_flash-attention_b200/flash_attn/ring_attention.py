@@ -111,6 +111,29 @@ class CudaBlockOps:
 
 _default_ops = None
 
+# Optional timeline of one call (tools/ring_probe.py): when set to a list, every phase appends (tag, step, start event,
+# end event), recorded on the compute stream -- a `wait_*` span is the time the compute stream stalled on a transfer.
+_trace = None
+
+
+class _span:
+    __slots__ = ("tag", "step", "e0")
+
+    def __init__(self, tag, step):
+        self.tag, self.step, self.e0 = tag, step, None
+
+    def __enter__(self):
+        if _trace is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+
+    def __exit__(self, *exc):
+        if self.e0 is not None:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            _trace.append((self.tag, self.step, self.e0, e1))
+        return False
+
 
 def _ops_or_default(ops):
     global _default_ops
@@ -125,7 +148,8 @@ def _ops_or_default(ops):
 # communication
 # ---------------------------------------------------------------------------------------------------------
 class _Ring:
-    """send to rank+1 / receive from rank-1, as one batched P2P so that NCCL pairs them without deadlock."""
+    """rank / neighbours of this process in `group`, and the batched send-to-next / receive-from-previous of the
+    torch.distributed transport (one batch so that NCCL pairs the two without deadlock)."""
 
     def __init__(self, group):
         self.group = group
@@ -155,9 +179,231 @@ class _Ring:
 
 
 # ---------------------------------------------------------------------------------------------------------
+# transports.  Both expose the same two objects to ring_forward / ring_backward:
+#   K/V stream        .k, .v (the block held now) | .prefetch(step): start moving the next block | .advance(): it is
+#                     current now (the compute stream is ordered after its arrival)
+#   dK/dV accumulator .cur fp32 (2, rows, h, d) of the block held now | .arrive(): the accumulator that follows this
+#                     block, one step behind, has come in | .depart(step): hand it on | .home(): the own block's sum
+# ---------------------------------------------------------------------------------------------------------
+class _DistKV:
+    """torch.distributed P2P (NCCL on GPUs, gloo in the CPU tests)."""
+
+    def __init__(self, ring, k_rows, v_rows):
+        self.ring = ring
+        self.kv = torch.stack([k_rows, v_rows])       # (2, rows, h, d): one message
+        self.nxt = torch.empty_like(self.kv)
+        self.reqs = []
+
+    k = property(lambda self: self.kv[0])
+    v = property(lambda self: self.kv[1])
+
+    def prefetch(self, step):
+        self.reqs = self.ring.exchange([self.kv], [self.nxt])
+
+    def advance(self):
+        self.ring.wait(self.reqs)
+        self.kv, self.nxt = self.nxt, self.kv
+
+
+class _DistDKV:
+    def __init__(self, ring, rows, h, d, device):
+        self.ring = ring
+        self.cur = torch.zeros(2, rows, h, d, dtype=torch.float32, device=device)
+        self.nxt = torch.empty_like(self.cur)
+        self.reqs = None
+
+    def arrive(self):
+        self.ring.wait(self.reqs)
+        self.cur, self.nxt = self.nxt, self.cur
+
+    def depart(self, step):
+        self.reqs = self.ring.exchange([self.cur], [self.nxt])
+
+    def home(self):
+        self.arrive()
+        return self.cur
+
+
+class DistTransport:
+    name = "dist"
+
+    def __init__(self, ring):
+        self.ring = ring
+
+    def kv_stream(self, k_rows, v_rows):
+        return _DistKV(self.ring, k_rows, v_rows)
+
+    def dkv_stream(self, rows, h, d, device):
+        return _DistDKV(self.ring, rows, h, d, device)
+
+
+_KV_READY, _KV_CONSUMED, _DKV_READY, _DKV_CONSUMED = 0, 1, 2, 3     # flag words (64 bytes apart)
+_FLAG_BYTES = 256
+
+
+class _PeerLink:
+    """Memory this rank shares with its ring neighbours through CUDA IPC, for one message shape:
+    [4 flag words | K/V buffer 0 | K/V buffer 1 | dK/dV buffer 0 | dK/dV buffer 1], the same layout on every rank.
+    Blocks are PULLED: a rank copies the block its predecessor holds out of the predecessor's buffer with a copy-engine
+    transfer over NVLink (measured 631 GB/s for 96 MiB on an 8 x B200 NVSwitch box; NCCL isend / irecv took a constant
+    ~0.6 ms per exchange, 83 - 163 GB/s, profiles/r02_ring_probe_n8.log).  Ordering across processes: monotone 64-bit
+    counters, never reset, written into the WAITER's memory (fa_flag_write) and waited for by a one-thread kernel on the
+    waiter's copy stream (fa_flag_wait_geq; traps after 20 s instead of hanging):
+        KV_READY      written by the predecessor: number of K/V blocks it has made available (cumulative over all calls)
+        KV_CONSUMED   written by the successor: number of pulls it has completed out of this rank's buffers
+        DKV_READY / DKV_CONSUMED   the same for the fp32 dK/dV accumulator that follows its block.
+    Calls are collective and identical on all ranks, so every rank derives the same counter values on the host."""
+
+    def __init__(self, ring, device, kv_bytes, dkv_bytes):
+        import flash_attn_cuda
+        assert ring.world > 1, "a ring of one has no peers (a process cannot map its own IPC handle)"
+        self.lib, self.ring, self.device = flash_attn_cuda, ring, device
+        self.kv_bytes, self.dkv_bytes = kv_bytes, dkv_bytes
+        self.kv_off = [_FLAG_BYTES, _FLAG_BYTES + kv_bytes]
+        self.dkv_off = [_FLAG_BYTES + 2 * kv_bytes, _FLAG_BYTES + 2 * kv_bytes + dkv_bytes]
+        self.mem = torch.empty(_FLAG_BYTES + 2 * kv_bytes + 2 * dkv_bytes, dtype=torch.uint8, device=device)
+        self.mem[:_FLAG_BYTES].zero_()
+        handles = [None] * ring.world
+        dist.all_gather_object(handles, flash_attn_cuda.ipc_export(self.mem), group=ring.group)
+        grank = {(dist.get_global_rank(ring.group, i) if ring.group is not None else i): i for i in range(ring.world)}
+        opened = {}                       # a handle may be mapped once per process: at world 2 both neighbours are the same rank
+        for peer in (ring.prev, ring.next):
+            if peer not in opened:
+                handle, offset = handles[grank[peer]]
+                opened[peer] = flash_attn_cuda.ipc_open(device, handle) + offset
+        self.prev_ptr, self.next_ptr = opened[ring.prev], opened[ring.next]      # addresses of the neighbours' `mem`
+        torch.cuda.synchronize(device)
+        dist.barrier(group=ring.group)                      # every flag word is zero before anybody writes one
+        self.s_kv, self.s_dkv = torch.cuda.Stream(device), torch.cuda.Stream(device)
+        self.kv_ready = self.kv_consumed = self.dkv_ready = self.dkv_consumed = 0     # cumulative, same on all ranks
+
+    def my_flag(self, word):
+        return self.mem.data_ptr() + 64 * word
+
+    def view(self, off, shape, dtype):
+        n = 1
+        for x in shape:
+            n *= x
+        return self.mem[off:off + n * torch.empty((), dtype=dtype).element_size()].view(dtype).view(shape)
+
+
+_links = {}
+
+
+class _PeerKV:
+    def __init__(self, link, k_rows, v_rows):
+        L = self.link = link
+        shape = (2,) + tuple(k_rows.shape)
+        self.buf = [L.view(L.kv_off[i], shape, k_rows.dtype) for i in (0, 1)]
+        self.idx, self.arrived = 0, None
+        self.R, self.C = L.kv_ready, L.kv_consumed
+        L.kv_ready += L.ring.world - 1           # a call announces world-1 blocks and pulls world-1 blocks
+        L.kv_consumed += L.ring.world - 1
+        # buffer 0 may still be the source of the successor's last pull of the previous call
+        with torch.cuda.stream(L.s_kv):
+            L.lib.flag_wait_geq(L.my_flag(_KV_CONSUMED), self.C, L.s_kv.cuda_stream)
+        torch.cuda.current_stream(L.device).wait_stream(L.s_kv)
+        self.buf[0][0].copy_(k_rows)
+        self.buf[0][1].copy_(v_rows)
+
+    k = property(lambda self: self.buf[self.idx][0])
+    v = property(lambda self: self.buf[self.idx][1])
+
+    def prefetch(self, t):
+        """pull the block the predecessor holds at step t into the other buffer (it is this rank's block of step t+1)"""
+        L, lib = self.link, self.link.lib
+        rs = L.s_kv.cuda_stream
+        # the target buffer was read by the kernels of step t-1; at t = 0 the fill of buffer 0 must have finished
+        L.s_kv.wait_stream(torch.cuda.current_stream(L.device))
+        if t == 0:
+            lib.flag_write(L.next_ptr + 64 * _KV_READY, self.R + 1, rs)           # my own K/V is block #0
+        lib.flag_wait_geq(L.my_flag(_KV_READY), self.R + t + 1, rs)              # the predecessor's block #t is there
+        lib.flag_wait_geq(L.my_flag(_KV_CONSUMED), self.C + t, rs)               # the successor is done with my target buffer
+        lib.peer_copy(self.buf[(t + 1) % 2].data_ptr(), L.prev_ptr + L.kv_off[t % 2], L.kv_bytes, rs)
+        if t + 1 <= L.ring.world - 2:
+            lib.flag_write(L.next_ptr + 64 * _KV_READY, self.R + t + 2, rs)       # block #(t+1) can be pulled from me
+        lib.flag_write(L.prev_ptr + 64 * _KV_CONSUMED, self.C + t + 1, rs)
+        self.arrived = torch.cuda.Event()
+        self.arrived.record(L.s_kv)
+
+    def advance(self):
+        torch.cuda.current_stream(self.link.device).wait_event(self.arrived)
+        self.idx ^= 1
+
+
+class _PeerDKV:
+    def __init__(self, link, rows, h, d):
+        L = self.link = link
+        self.buf = [L.view(L.dkv_off[i], (2, rows, h, d), torch.float32) for i in (0, 1)]
+        self.idx, self.arrived = 0, None
+        self.R, self.C = L.dkv_ready, L.dkv_consumed
+        L.dkv_ready += L.ring.world              # world announcements and world pulls per call (the last one goes home)
+        L.dkv_consumed += L.ring.world
+        with torch.cuda.stream(L.s_dkv):
+            L.lib.flag_wait_geq(L.my_flag(_DKV_CONSUMED), self.C, L.s_dkv.cuda_stream)
+        torch.cuda.current_stream(L.device).wait_stream(L.s_dkv)
+        self.buf[0].zero_()
+
+    cur = property(lambda self: self.buf[self.idx])
+
+    def depart(self, t):
+        """step t's sums are in `cur`: announce them to the successor, and pull the predecessor's (the accumulator of the
+        block this rank holds at step t+1) under the next step's kernel"""
+        L, lib = self.link, self.link.lib
+        rs = L.s_dkv.cuda_stream
+        L.s_dkv.wait_stream(torch.cuda.current_stream(L.device))                     # the accumulate kernels of step t
+        lib.flag_write(L.next_ptr + 64 * _DKV_READY, self.R + t + 1, rs)
+        lib.flag_wait_geq(L.my_flag(_DKV_READY), self.R + t + 1, rs)
+        lib.flag_wait_geq(L.my_flag(_DKV_CONSUMED), self.C + t, rs)              # the successor has pulled what my target buffer held
+        lib.peer_copy(self.buf[(t + 1) % 2].data_ptr(), L.prev_ptr + L.dkv_off[t % 2], L.dkv_bytes, rs)
+        lib.flag_write(L.prev_ptr + 64 * _DKV_CONSUMED, self.C + t + 1, rs)
+        self.arrived = torch.cuda.Event()
+        self.arrived.record(L.s_dkv)
+
+    def arrive(self):
+        torch.cuda.current_stream(self.link.device).wait_event(self.arrived)
+        self.idx ^= 1
+
+    def home(self):
+        self.arrive()
+        return self.cur
+
+
+class PeerTransport:
+    name = "peer"
+
+    def __init__(self, ring, device, rows, h, d, dtype):
+        es = torch.empty((), dtype=dtype).element_size()
+        key = (id(ring.group), ring.world, ring.rank, device.index, rows, h, d, dtype)
+        if key not in _links:
+            _links[key] = _PeerLink(ring, device, 2 * rows * h * d * es, 2 * rows * h * d * 4)
+        self.link = _links[key]
+
+    def kv_stream(self, k_rows, v_rows):
+        return _PeerKV(self.link, k_rows, v_rows)
+
+    def dkv_stream(self, rows, h, d, device):
+        return _PeerDKV(self.link, rows, h, d)
+
+
+default_transport = None      # None = "peer" for CUDA tensors on an NCCL group of more than one rank, else "dist"
+
+
+def _make_transport(ring, q, rows, transport):
+    transport = transport or default_transport
+    if transport is None:
+        peer_ok = q.is_cuda and ring.world > 1 and dist.is_initialized() and dist.get_backend(ring.group) == "nccl"
+        transport = "peer" if peer_ok else "dist"
+    if transport == "peer" and ring.world > 1:
+        return PeerTransport(ring, q.device, rows, q.shape[-2], q.shape[-1], q.dtype)
+    assert transport in ("dist", "peer"), f"unknown ring transport {transport!r}"
+    return DistTransport(ring)
+
+
+# ---------------------------------------------------------------------------------------------------------
 # forward / backward
 # ---------------------------------------------------------------------------------------------------------
-def ring_forward(q, k, v, softmax_scale, group=None, ops=None):
+def ring_forward(q, k, v, softmax_scale, group=None, ops=None, transport=None):
     """q, k, v: local (b, 2, c, h, d) zig-zag shards.  -> out (b, 2, c, h, d) (dtype of q), lse (b, h, 2c) fp32."""
     ops = _ops_or_default(ops)
     ring = _Ring(group)
@@ -168,20 +414,22 @@ def ring_forward(q, k, v, softmax_scale, group=None, ops=None):
     qf = q.reshape(rows, h, d)
     o_acc = torch.empty(rows, h, d, dtype=torch.float32, device=q.device)
     lse_acc = torch.empty(b, h, 2 * c, dtype=torch.float32, device=q.device)
-    kv = torch.stack([k.reshape(rows, h, d), v.reshape(rows, h, d)])       # (2, b*2c, h, d): one message
-    kv_next = torch.empty_like(kv)
+    kvs = _make_transport(ring, q, rows, transport).kv_stream(k.reshape(rows, h, d), v.reshape(rows, h, d))
     for step in range(ring.world):
-        reqs = ring.exchange([kv], [kv_next]) if step + 1 < ring.world else []   # the next block moves under this step's kernel
+        more = step + 1 < ring.world
+        if more:
+            kvs.prefetch(step)          # the next block moves under this step's kernel
         plan = _step_plan(step, ring.rank, ring.world)
-        o_blk, lse_blk = ops.fwd(qf, kv[0], kv[1], b, c, plan, softmax_scale)
-        ops.merge(o_acc, lse_acc, o_blk, lse_blk, b, c, plan, step == 0)
-        if reqs:
-            ring.wait(reqs)
-            kv, kv_next = kv_next, kv
+        with _span("fwd_kernels", step):
+            o_blk, lse_blk = ops.fwd(qf, kvs.k, kvs.v, b, c, plan, softmax_scale)
+            ops.merge(o_acc, lse_acc, o_blk, lse_blk, b, c, plan, step == 0)
+        if more:
+            with _span("fwd_wait_kv", step):
+                kvs.advance()
     return o_acc.to(q.dtype).reshape(b, 2, c, h, d), lse_acc
 
 
-def ring_backward(dout, q, k, v, out, lse, softmax_scale, group=None, ops=None):
+def ring_backward(dout, q, k, v, out, lse, softmax_scale, group=None, ops=None, transport=None):
     """-> dq, dk, dv, each (b, 2, c, h, d) in the dtype of q.  `lse` is ring_forward's (b, h, 2c) final log-sum-exp."""
     ops = _ops_or_default(ops)
     ring = _Ring(group)
@@ -189,48 +437,52 @@ def ring_backward(dout, q, k, v, out, lse, softmax_scale, group=None, ops=None):
     rows = b * 2 * c
     qf, of, gf = (t.reshape(rows, h, d) for t in (q, out, dout.contiguous()))
     dq_acc = torch.zeros(rows, h, d, dtype=torch.float32, device=q.device)
-    kv = torch.stack([k.reshape(rows, h, d), v.reshape(rows, h, d)])
-    dkv = torch.zeros(2, rows, h, d, dtype=torch.float32, device=q.device)       # follows its K/V block, one step behind
-    kv_next, dkv_next = torch.empty_like(kv), torch.empty_like(dkv)
-    g_reqs = None
+    tr = _make_transport(ring, q, rows, transport)
+    kvs = tr.kv_stream(k.reshape(rows, h, d), v.reshape(rows, h, d))
+    acc = tr.dkv_stream(rows, h, d, q.device)       # follows its K/V block around the ring, one step behind
     for step in range(ring.world):
-        kv_reqs = ring.exchange([kv], [kv_next]) if step + 1 < ring.world else []
+        more = step + 1 < ring.world
+        if more:
+            kvs.prefetch(step)
         plan = _step_plan(step, ring.rank, ring.world)
         q_off, q_len, k_len, _ = plan
-        dq_blk, dk_blk, dv_blk = ops.bwd(gf, qf, kv[0], kv[1], of, lse, b, c, plan, softmax_scale)
-        ops.accumulate(dq_acc, dq_blk, b, c, q_off, q_len)
-        if g_reqs is not None:          # the accumulator of the block held now was sent by the previous rank a step ago
-            ring.wait(g_reqs)
-            dkv, dkv_next = dkv_next, dkv
-        ops.accumulate(dkv[0], dk_blk, b, c, 0, k_len)
-        ops.accumulate(dkv[1], dv_blk, b, c, 0, k_len)
-        g_reqs = ring.exchange([dkv], [dkv_next])   # travels under the next step's kernel; after the last step it goes home
-        if kv_reqs:
-            ring.wait(kv_reqs)
-            kv, kv_next = kv_next, kv
-    ring.wait(g_reqs)
-    dkv = dkv_next
+        with _span("bwd_kernels", step):
+            dq_blk, dk_blk, dv_blk = ops.bwd(gf, qf, kvs.k, kvs.v, of, lse, b, c, plan, softmax_scale)
+            ops.accumulate(dq_acc, dq_blk, b, c, q_off, q_len)
+        if step > 0:                    # the accumulator of the block held now left the previous rank a step ago
+            with _span("bwd_wait_dkv", step):
+                acc.arrive()
+        with _span("bwd_accumulate", step):
+            ops.accumulate(acc.cur[0], dk_blk, b, c, 0, k_len)
+            ops.accumulate(acc.cur[1], dv_blk, b, c, 0, k_len)
+        acc.depart(step)                # travels under the next step's kernel; after the last step it goes home
+        if more:
+            with _span("bwd_wait_kv", step):
+                kvs.advance()
+    with _span("bwd_wait_dkv", ring.world):
+        dkv = acc.home()
     shape = (b, 2, c, h, d)
     return dq_acc.to(q.dtype).reshape(shape), dkv[0].to(q.dtype).reshape(shape), dkv[1].to(q.dtype).reshape(shape)
 
 
 class RingFlashAttnFunc(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, q, k, v, softmax_scale, group, ops):
+    def forward(ctx, q, k, v, softmax_scale, group, ops, transport):
         softmax_scale = q.shape[-1] ** (-0.5) if softmax_scale is None else softmax_scale
-        out, lse = ring_forward(q, k, v, softmax_scale, group, ops)
+        out, lse = ring_forward(q, k, v, softmax_scale, group, ops, transport)
         ctx.save_for_backward(q, k, v, out, lse)
-        ctx.softmax_scale, ctx.group, ctx.ops = softmax_scale, group, ops
+        ctx.softmax_scale, ctx.group, ctx.ops, ctx.transport = softmax_scale, group, ops, transport
         return out
 
     @staticmethod
     def backward(ctx, dout):
         q, k, v, out, lse = ctx.saved_tensors
-        dq, dk, dv = ring_backward(dout, q, k, v, out, lse, ctx.softmax_scale, ctx.group, ctx.ops)
-        return dq, dk, dv, None, None, None
+        dq, dk, dv = ring_backward(dout, q, k, v, out, lse, ctx.softmax_scale, ctx.group, ctx.ops, ctx.transport)
+        return dq, dk, dv, None, None, None, None
 
 
-def ring_flash_attn_func(q, k, v, softmax_scale=None, group=None, ops=None):
+def ring_flash_attn_func(q, k, v, softmax_scale=None, group=None, ops=None, transport=None):
     """Causal attention over a sequence sharded zig-zag across the ranks of `group`.
-    q, k, v: local (b, 2, c, h, d) shards (see zigzag_shard).  Returns the local (b, 2, c, h, d) output shard."""
-    return RingFlashAttnFunc.apply(q, k, v, softmax_scale, group, ops)
+    q, k, v: local (b, 2, c, h, d) shards (see zigzag_shard).  Returns the local (b, 2, c, h, d) output shard.
+    transport: "peer" (CUDA-IPC peer memory over NVLink; the default on GPUs), "dist" (torch.distributed P2P) or None."""
+    return RingFlashAttnFunc.apply(q, k, v, softmax_scale, group, ops, transport)

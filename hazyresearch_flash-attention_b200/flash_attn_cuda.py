@@ -80,6 +80,20 @@ def _load_library():
     lib.fa_rotary_qk.restype = ctypes.c_int
     lib.fa_rotary_qk.argtypes = ([ctypes.c_void_p] * 4 + [ctypes.c_int64] + [ctypes.c_int32] * 5 + [ctypes.c_int64] * 2
                                  + [ctypes.c_int32] * 2 + [ctypes.c_void_p])
+    lib.fa_flag_write.restype = ctypes.c_int
+    lib.fa_flag_write.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p]
+    lib.fa_flag_wait_geq.restype = ctypes.c_int
+    lib.fa_flag_wait_geq.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_void_p]
+    lib.fa_ipc_export.restype = ctypes.c_int
+    lib.fa_ipc_export.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64)]
+    lib.fa_ipc_open.restype = ctypes.c_int
+    lib.fa_ipc_open.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]
+    lib.fa_ipc_close.restype = ctypes.c_int
+    lib.fa_ipc_close.argtypes = [ctypes.c_void_p]
+    lib.fa_enable_peer_access.restype = ctypes.c_int
+    lib.fa_enable_peer_access.argtypes = [ctypes.c_int32]
+    lib.fa_peer_copy.restype = ctypes.c_int
+    lib.fa_peer_copy.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p]
     lib.fa_dropout_keep8_host.restype = None
     lib.fa_dropout_keep8_host.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint32,
                                           ctypes.c_uint32, ctypes.c_float, ctypes.c_void_p]
@@ -526,6 +540,41 @@ def accumulate_f32(dst, src, n_batches, run_elems, dst_batch_stride, src_batch_s
         rc = _lib.fa_accumulate_f32(_ptr(dst), _ptr(src), n_batches, run_elems, dst_batch_stride, src_batch_stride,
                                     1 if src.dtype == torch.bfloat16 else 0, guard.raw_stream())
     _raise_if_failed(rc, "fa_accumulate_f32")
+
+
+def flag_write(flag_ptr, value, raw_stream):
+    """fa_flag_write on a raw stream handle; flag_ptr: device address (possibly in a peer GPU's memory)."""
+    _raise_if_failed(_lib.fa_flag_write(flag_ptr, value, raw_stream), "fa_flag_write")
+
+
+def flag_wait_geq(flag_ptr, value, raw_stream, timeout_ms=0):
+    _raise_if_failed(_lib.fa_flag_wait_geq(flag_ptr, value, timeout_ms, raw_stream), "fa_flag_wait_geq")
+
+
+def ipc_export(tensor):
+    """-> (64-byte handle of the cudaMalloc allocation containing `tensor`, byte offset of the tensor in it)"""
+    buf, off = (ctypes.c_uint8 * 64)(), ctypes.c_uint64()
+    with _DeviceGuard(tensor.device):
+        _raise_if_failed(_lib.fa_ipc_export(tensor.data_ptr(), buf, ctypes.byref(off)), "fa_ipc_export")
+    return bytes(buf), off.value
+
+
+def ipc_open(device, handle):
+    """map another process's allocation into `device`'s address space -> base address (int)"""
+    buf, base = (ctypes.c_uint8 * 64).from_buffer_copy(handle), ctypes.c_void_p()
+    with _DeviceGuard(device):
+        _raise_if_failed(_lib.fa_ipc_open(buf, ctypes.byref(base)), "fa_ipc_open")
+    return base.value
+
+
+def enable_peer_access(device, peer_index):
+    """let kernels and copies of `device` reach memory of GPU `peer_index` directly (fa_enable_peer_access)"""
+    with _DeviceGuard(device):
+        _raise_if_failed(_lib.fa_enable_peer_access(peer_index), "fa_enable_peer_access")
+
+
+def peer_copy(dst_ptr, src_ptr, nbytes, raw_stream):
+    _raise_if_failed(_lib.fa_peer_copy(dst_ptr, src_ptr, nbytes, raw_stream), "fa_peer_copy")
 
 
 def rotary_qk(qkv_in, qkv_out, cos, sin, seqlen, n_rot=2, conjugate=False):

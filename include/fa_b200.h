@@ -184,6 +184,29 @@ int fa_merge_partials(float* o_acc, float* lse_acc, const void* o_blk, const flo
 int fa_accumulate_f32(float* dst, const void* src, int64_t n_batches, int64_t run_elems, int64_t dst_batch_stride,
                       int64_t src_batch_stride, int32_t is_bf16, void* stream);
 
+/* Peer-memory transport of the K/V ring (flash_attn/ring_attention.py; no counterpart in the single-GPU reference).
+ * One process per GPU; every rank maps its neighbours' buffers and flag words through CUDA IPC.  Blocks move as copy-
+ * engine transfers over NVLink on the caller's stream; ordering across processes goes through monotone 64-bit counters:
+ *   fa_flag_write    *flag = value, published with a system-scope fence after everything already enqueued on `stream`
+ *                    (flag may live in a peer GPU's memory);
+ *   fa_flag_wait_geq holds `stream` until *flag >= value (a one-thread spin kernel; flag should be in LOCAL memory).  If
+ *                    that does not happen within timeout_ms (0 = 20 s) the kernel traps: a lost peer surfaces as a CUDA
+ *                    error on this stream, never as a hung GPU;
+ *   fa_peer_copy     cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, stream) -- either pointer may be peer memory;
+ *   fa_enable_peer_access  cudaDeviceEnablePeerAccess(peer_device) for the current device (idempotent): needed before this
+ *                    device's kernels write a peer's flag word; FA_ERR_UNSUPPORTED_DEVICE if there is no P2P path. */
+int fa_enable_peer_access(int32_t peer_device);
+/* CUDA IPC: fa_ipc_export names the cudaMalloc allocation that contains `ptr` (64-byte handle) and ptr's offset in it;
+ * fa_ipc_open maps such an allocation of ANOTHER process into the current device's address space (peer access to the
+ * exporting GPU is enabled with it) -- open a given handle once per process; fa_ipc_close unmaps.  The exporter must
+ * keep the allocation alive while it is mapped elsewhere. */
+int fa_ipc_export(const void* ptr, uint8_t handle[64], uint64_t* offset);
+int fa_ipc_open(const uint8_t handle[64], void** base);
+int fa_ipc_close(void* base);
+int fa_flag_write(uint64_t* flag, uint64_t value, void* stream);
+int fa_flag_wait_geq(const uint64_t* flag, uint64_t value, uint64_t timeout_ms, void* stream);
+int fa_peer_copy(void* dst, const void* src, uint64_t bytes, void* stream);
+
 /* Rotary position embedding of the first n_rot parts (q, k) of a packed (n_rows, n_parts, h, d) 16-bit tensor in one
  * pass -- replaces the pure-PyTorch apply_rotary_pos_emb + torch.stack the reference runs before attention in FlashMHA
  * (flash_attn/rotary.py:21-42, flash_attn/flash_attention.py:105-110).  Interleaved pairs:
