@@ -127,8 +127,13 @@ __global__ void gather_rows_kernel(V* __restrict__ dst, const V* __restrict__ sr
                                    int64_t n, int64_t row_vecs) {
   // one CTA row-group per blockIdx.y-strided index; threads stride over the row's vectors
   for (int64_t i = blockIdx.x; i < n; i += gridDim.x) {
-    const V* s = src + idx[i] * row_vecs;
+    const int64_t r = idx[i];
     V* d = dst + i * row_vecs;
+    if (r < 0) {                                   // padding entry of a sync-free index list (fa_varlen_index): a zero row
+      for (int64_t c = threadIdx.x; c < row_vecs; c += blockDim.x) d[c] = V{};
+      continue;
+    }
+    const V* s = src + r * row_vecs;
     for (int64_t c = threadIdx.x; c < row_vecs; c += blockDim.x) d[c] = __ldg(s + c);
   }
 }
@@ -136,9 +141,119 @@ template <typename V>
 __global__ void scatter_rows_kernel(V* __restrict__ dst, const V* __restrict__ src, const int64_t* __restrict__ idx,
                                     int64_t n, int64_t row_vecs) {
   for (int64_t i = blockIdx.x; i < n; i += gridDim.x) {
+    const int64_t r = idx[i];
+    if (r < 0) continue;                           // padding entry: no destination row
     const V* s = src + i * row_vecs;
-    V* d = dst + idx[i] * row_vecs;
+    V* d = dst + r * row_vecs;
     for (int64_t c = threadIdx.x; c < row_vecs; c += blockDim.x) d[c] = __ldg(s + c);
+  }
+}
+
+// dst[idx[i], :] += src[i, :] (indices unique, negative = skip): the backward of IndexFirstAxisResidual
+// (flash_attn/bert_padding.py:67-96, `grad_residual.index_add`).  kind 0 = fp16, 1 = bf16, 2 = fp32; 16 bytes per thread.
+template <int kKind>
+__global__ void scatter_add_rows_kernel(void* __restrict__ dst_, const void* __restrict__ src_, const int64_t* __restrict__ idx,
+                                        int64_t n, int64_t row_vecs) {
+  uint4* dst = reinterpret_cast<uint4*>(dst_);
+  const uint4* src = reinterpret_cast<const uint4*>(src_);
+  for (int64_t i = blockIdx.x; i < n; i += gridDim.x) {
+    const int64_t r = idx[i];
+    if (r < 0) continue;
+    for (int64_t c = threadIdx.x; c < row_vecs; c += blockDim.x) {
+      uint4 a = dst[r * row_vecs + c];
+      const uint4 b = __ldg(src + i * row_vecs + c);
+      if (kKind == 2) {
+        float* x = reinterpret_cast<float*>(&a);
+        const float* y = reinterpret_cast<const float*>(&b);
+#pragma unroll
+        for (int t = 0; t < 4; ++t) x[t] += y[t];
+      } else {
+        using T = typename Elem<kKind == 1>::T;
+        T* x = reinterpret_cast<T*>(&a);
+        const T* y = reinterpret_cast<const T*>(&b);
+#pragma unroll
+        for (int t = 0; t < 8; ++t) x[t] = Elem<kKind == 1>::from_float(Elem<kKind == 1>::to_float(x[t]) + Elem<kKind == 1>::to_float(y[t]));
+      }
+      dst[r * row_vecs + c] = a;
+    }
+  }
+}
+
+// ---- fa_varlen_index: (batch, seqlen) 0/1 byte mask -> indices of the valid tokens, cu_seqlens, max_seqlen, all on the
+// device (the reference does nonzero() + .item(): a host round trip per call, flash_attn/bert_padding.py:99-119). ----
+__global__ void __launch_bounds__(256) varlen_count_kernel(const uint8_t* __restrict__ mask, int s, int32_t* __restrict__ cu_seqlens) {
+  __shared__ int warp_sums[8];
+  const uint8_t* row = mask + (int64_t)blockIdx.x * s;
+  int n = 0;
+  for (int j = threadIdx.x; j < s; j += 256) n += row[j] != 0;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+  if ((threadIdx.x & 31) == 0) warp_sums[threadIdx.x >> 5] = n;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int w = 0; w < 8; ++w) t += warp_sums[w];
+    cu_seqlens[blockIdx.x + 1] = t;                // the length for now; varlen_scan_kernel turns it into the prefix sum
+  }
+}
+__global__ void __launch_bounds__(1024) varlen_scan_kernel(int32_t* __restrict__ cu_seqlens, int b, int32_t* __restrict__ stats) {
+  __shared__ int warp_tot[32];
+  __shared__ int warp_max[32];
+  __shared__ int carry_s, max_s;
+  if (threadIdx.x == 0) { carry_s = 0; max_s = 0; cu_seqlens[0] = 0; }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int base = 0; base < b; base += 1024) {
+    const int i = base + threadIdx.x;
+    const int len = i < b ? cu_seqlens[i + 1] : 0;
+    int incl = len, mx = len;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int up = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += up;
+      mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    if (lane == 31) warp_tot[warp] = incl;
+    if (lane == 0) warp_max[warp] = mx;
+    __syncthreads();
+    int before = carry_s;
+    for (int w = 0; w < warp; ++w) before += warp_tot[w];
+    if (i < b) cu_seqlens[i + 1] = before + incl;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int t = 0, m = max_s;
+      for (int w = 0; w < 32; ++w) { t += warp_tot[w]; m = max(m, warp_max[w]); }
+      carry_s += t;
+      max_s = m;
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { stats[0] = max_s; stats[1] = carry_s; }
+}
+__global__ void __launch_bounds__(256) varlen_indices_kernel(const uint8_t* __restrict__ mask, int s, const int32_t* __restrict__ cu_seqlens,
+                                                             int64_t* __restrict__ indices) {
+  __shared__ int warp_cnt[8];
+  __shared__ int carry_s;
+  const int64_t row0 = (int64_t)blockIdx.x * s;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry_s = cu_seqlens[blockIdx.x];
+  __syncthreads();
+  for (int base = 0; base < s; base += 256) {
+    const int j = base + threadIdx.x;
+    const bool on = j < s && mask[row0 + j] != 0;
+    const uint32_t ball = __ballot_sync(0xffffffffu, on);
+    if (lane == 0) warp_cnt[warp] = __popc(ball);
+    __syncthreads();
+    int before = carry_s;
+    for (int w = 0; w < warp; ++w) before += warp_cnt[w];
+    if (on) indices[before + __popc(ball & ((1u << lane) - 1u))] = row0 + j;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int t = 0;
+      for (int w = 0; w < 8; ++w) t += warp_cnt[w];
+      carry_s += t;
+    }
+    __syncthreads();
   }
 }
 
@@ -701,6 +816,46 @@ int fa_gather_rows(void* dst, const void* src, const int64_t* indices, int64_t n
 int fa_scatter_rows(void* dst, const void* src, const int64_t* indices, int64_t n_indices, int64_t row_bytes, void* stream) {
   fa::g_last_error[0] = 0;
   return fa::move_rows<false>(dst, src, indices, n_indices, row_bytes, stream);
+}
+
+int fa_scatter_add_rows(void* dst, const void* src, const int64_t* indices, int64_t n_indices, int64_t row_bytes, int32_t kind,
+                        void* stream) {
+  fa::g_last_error[0] = 0;
+  if (n_indices < 0 || row_bytes < 0 || kind < 0 || kind > 2) return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_scatter_add_rows: bad size or kind");
+  if (n_indices == 0 || row_bytes == 0) return FA_OK;
+  if (!dst || !src || !indices || !fa::aligned16(dst) || !fa::aligned16(src) || row_bytes % 16 != 0)
+    return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_scatter_add_rows: pointers must be 16-byte aligned and rows a multiple of 16 bytes (got %lld)",
+                    (long long)row_bytes);
+  int rc = fa::check_device();
+  if (rc != FA_OK) return rc;
+  const int64_t vecs = row_bytes / 16;
+  int threads = 32;
+  while (threads < 256 && threads < vecs) threads *= 2;
+  const unsigned grid = static_cast<unsigned>(n_indices < 148 * 16 ? n_indices : 148 * 16);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (kind == 0) fa::scatter_add_rows_kernel<0><<<grid, threads, 0, st>>>(dst, src, indices, n_indices, vecs);
+  else if (kind == 1) fa::scatter_add_rows_kernel<1><<<grid, threads, 0, st>>>(dst, src, indices, n_indices, vecs);
+  else fa::scatter_add_rows_kernel<2><<<grid, threads, 0, st>>>(dst, src, indices, n_indices, vecs);
+  fa::count_launch();
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? FA_OK : fa::cuda_fail(e, "scatter_add_rows launch");
+}
+
+int fa_varlen_index(const uint8_t* mask, int32_t b, int32_t s, int64_t* indices, int32_t* cu_seqlens, int32_t* stats, void* stream) {
+  fa::g_last_error[0] = 0;
+  if (b <= 0 || s <= 0) return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_varlen_index: batch and seqlen must be positive (got %d x %d)", b, s);
+  if (!mask || !indices || !cu_seqlens || !stats) return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_varlen_index: NULL pointer");
+  int rc = fa::check_device();
+  if (rc != FA_OK) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaError_t e = cudaMemsetAsync(indices, 0xFF, (size_t)b * s * sizeof(int64_t), st);     // -1 = "no token": entries past the total
+  if (e != cudaSuccess) return fa::cuda_fail(e, "cudaMemsetAsync(indices)");
+  fa::varlen_count_kernel<<<b, 256, 0, st>>>(mask, s, cu_seqlens);
+  fa::varlen_scan_kernel<<<1, 1024, 0, st>>>(cu_seqlens, b, stats);
+  fa::varlen_indices_kernel<<<b, 256, 0, st>>>(mask, s, cu_seqlens, indices);
+  fa::count_launch(); fa::count_launch(); fa::count_launch();
+  e = cudaGetLastError();
+  return e == cudaSuccess ? FA_OK : fa::cuda_fail(e, "varlen_index launch");
 }
 
 int fa_rotary_qk(const void* in, void* out, const float* cos_t, const float* sin_t, int64_t n_rows, int32_t seqlen, int32_t n_parts,

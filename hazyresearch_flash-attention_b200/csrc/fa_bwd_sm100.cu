@@ -790,22 +790,29 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
       if (wq == 0) FA_TRACE(10 + 4 * g);
       tc_fence_after();
       if (it > 0) mbar_wait(ds_empty, (it - 1) & 1);   // dK / dQ MMAs of the previous tile have read sDs
+      // dP^T comes out of TMEM in one go without dropout; the dropout variants, which also hold the keep bits and run out of
+      // registers (pf[64] + dpr[64] live at once spilled 70 values per tile in this loop), take it one 32-column half at a
+      // time so that the two halves share registers -- one more TMEM round trip per tile in an issue-bound variant
+      constexpr bool kSplitDp = kDropout;
       uint32_t dpr[2][32];
-      tmem_ld32(tDP, dpr[0]);
-      tmem_ld32(tDP + 32, dpr[1]);
-      tmem_wait_ld();
-      if (need_mask) {
-        // masked entries: P is exactly 0 there, but dP may be anything (stray rows of a partial tile) and 0 * NaN = NaN
+      if constexpr (!kSplitDp) {
+        tmem_ld32(tDP, dpr[0]);
+        tmem_ld32(tDP + 32, dpr[1]);
+        tmem_wait_ld();
+      }
 #pragma unroll
-        for (int ch = 0; ch < 2; ++ch) {
+      for (int ch = 0; ch < 2; ++ch) {
+        if constexpr (kSplitDp) {
+          tmem_ld32(tDP + ch * 32, dpr[ch]);
+          tmem_wait_ld();
+        }
+        if (need_mask) {
+          // masked entries: P is exactly 0 there, but dP may be anything (stray rows of a partial tile) and 0 * NaN = NaN
           const uint32_t mb = static_cast<uint32_t>(colmask >> (ch * 32));
 #pragma unroll
           for (int c = 0; c < 32; ++c)
             if (!((mb >> c) & 1u)) dpr[ch][c] = 0u;
         }
-      }
-#pragma unroll
-      for (int ch = 0; ch < 2; ++ch) {
         uint32_t dsp[16];
         const uint32_t kb = static_cast<uint32_t>(keepbits >> (ch * 32));
 #pragma unroll
@@ -1156,6 +1163,9 @@ cudaError_t launch_bwd_sm100(const fa_params& p, const BlockMaskView& bm, void* 
       e = launch_bwd_variant<128, true, true, false, false, false>(maps, p, bm, ws, stream);
     else if (p.d > 64 && p.is_bf16 && !p.is_causal && !(p.p_dropout > 0.f) && bm.dense == nullptr && p.alibi_slopes == nullptr)
       e = launch_bwd_variant<128, true, false, false, false, false>(maps, p, bm, ws, stream);
+    else if (p.d <= 64 && !p.is_bf16 && p.is_causal && bm.dense == nullptr && p.alibi_slopes == nullptr)
+      e = p.p_dropout > 0.f ? launch_bwd_variant<64, false, true, true, false, false>(maps, p, bm, ws, stream)
+                            : launch_bwd_variant<64, false, true, false, false, false>(maps, p, bm, ws, stream);
     else e = cudaErrorNotSupported;
 #else
     if (p.d <= 64) e = p.is_bf16 ? dispatch_bwd_flags<64, true>(maps, p, bm, ws, stream) : dispatch_bwd_flags<64, false>(maps, p, bm, ws, stream);

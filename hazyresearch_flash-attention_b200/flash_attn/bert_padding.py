@@ -96,7 +96,13 @@ class IndexFirstAxisResidual(torch.autograd.Function):
         indices, = ctx.saved_tensors
         assert grad_output.ndim >= 2
         assert grad_residual.shape[1:] == grad_output.shape[1:]
-        grad_input = grad_residual.index_add(0, indices, grad_output)
+        g2d, r2d = _flatten_rows(grad_output), _flatten_rows(grad_residual)
+        if (_use_kernels(g2d, indices) and g2d.dtype == r2d.dtype and g2d.dtype in (torch.float16, torch.bfloat16, torch.float32)
+                and (g2d.shape[1] * g2d.element_size()) % 16 == 0):
+            import flash_attn_cuda
+            grad_input = flash_attn_cuda.scatter_add_rows(r2d.clone(), g2d.contiguous(), indices.contiguous())
+        else:
+            grad_input = r2d.index_add(0, indices, g2d)
         return grad_input.reshape(ctx.first_axis_dim, *grad_output.shape[1:]), None
 
 
@@ -114,6 +120,24 @@ def unpad_input(hidden_states, attention_mask):
     cu_seqlens = F.pad(torch.cumsum(seqlens_in_batch, dim=0, dtype=torch.int32), (1, 0))
     flat = hidden_states.reshape(hidden_states.shape[0] * hidden_states.shape[1], *hidden_states.shape[2:])
     return index_first_axis(flat, indices), indices, cu_seqlens, max_seqlen_in_batch
+
+
+def unpad_input_nosync(hidden_states, attention_mask):
+    """unpad_input without the host round trip (the reference synchronises twice per call: nonzero() and .item(),
+    reference :109-112).  CUDA only.  Same 4-tuple, with upper bounds where the reference has exact values:
+
+      hidden_states  (batch * seqlen, ...): the valid tokens first, in order; the remaining rows are zero
+      indices        (batch * seqlen,) int64: positions of the valid tokens, then -1 (pad_input and the gradients skip them)
+      cu_seqlens     (batch + 1,) int32, exact, on the device
+      max_seqlen     `seqlen` (python int): an upper bound, which is all the attention kernels need
+
+    Everything downstream (flash_attn_unpadded_*_func, pad_input, autograd) gives the same result for the valid tokens."""
+    import flash_attn_cuda
+    assert hidden_states.is_cuda and attention_mask.is_cuda, "unpad_input_nosync is the CUDA path; use unpad_input on CPU"
+    batch, seqlen = attention_mask.shape
+    indices, cu_seqlens, _ = flash_attn_cuda.varlen_index(attention_mask)
+    flat = hidden_states.reshape(batch * seqlen, *hidden_states.shape[2:])
+    return index_first_axis(flat, indices), indices, cu_seqlens, seqlen
 
 
 def pad_input(hidden_states, indices, batch, seqlen):

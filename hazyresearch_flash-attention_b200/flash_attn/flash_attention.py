@@ -8,7 +8,7 @@ because the kernels support both and the headline d=128 configuration is bf16.
 import torch
 import torch.nn as nn
 
-from flash_attn.bert_padding import pad_input, unpad_input
+from flash_attn.bert_padding import pad_input, unpad_input_nosync
 from flash_attn.flash_attn_interface import flash_attn_unpadded_qkvpacked_func
 from flash_attn.rotary import RotaryEmbedding, RotaryEmbedding2D, apply_rotary_qkvpacked_, rotary_tables
 
@@ -45,7 +45,9 @@ class FlashAttention(nn.Module):
                                                      causal=causal)
             return out.reshape(batch, seqlen, *out.shape[1:]), None
         nheads, headdim = qkv.shape[-2], qkv.shape[-1]
-        x_unpad, indices, cu, max_s = unpad_input(qkv.reshape(batch, seqlen, 3 * nheads * headdim), key_padding_mask)
+        # indices / cu_seqlens are built on the device: no host synchronisation anywhere in this module (the reference
+        # synchronises twice here, bert_padding.py:109-112); max_s is the padded length, an upper bound
+        x_unpad, indices, cu, max_s = unpad_input_nosync(qkv.reshape(batch, seqlen, 3 * nheads * headdim), key_padding_mask)
         out_unpad = flash_attn_unpadded_qkvpacked_func(x_unpad.reshape(-1, 3, nheads, headdim), cu, max_s, p,
                                                        softmax_scale=self.softmax_scale, causal=causal)
         out = pad_input(out_unpad.reshape(-1, nheads * headdim), indices, batch, seqlen)

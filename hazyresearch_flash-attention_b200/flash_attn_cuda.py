@@ -84,6 +84,12 @@ def _load_library():
     lib.fa_flag_write.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p]
     lib.fa_flag_wait_geq.restype = ctypes.c_int
     lib.fa_flag_wait_geq.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_void_p]
+    lib.fa_scatter_add_rows.restype = ctypes.c_int
+    lib.fa_scatter_add_rows.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64,
+                                        ctypes.c_int32, ctypes.c_void_p]
+    lib.fa_varlen_index.restype = ctypes.c_int
+    lib.fa_varlen_index.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p,
+                                    ctypes.c_void_p, ctypes.c_void_p]
     lib.fa_ipc_export.restype = ctypes.c_int
     lib.fa_ipc_export.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64)]
     lib.fa_ipc_open.restype = ctypes.c_int
@@ -510,6 +516,36 @@ def scatter_rows(src2d, indices, first_axis_dim, out=None):
         rc = _lib.fa_scatter_rows(_ptr(out), _ptr(src2d), _ptr(indices), indices.numel(), row_bytes, guard.raw_stream())
     _raise_if_failed(rc, "fa_scatter_rows")
     return out
+
+
+_KIND = {torch.float16: 0, torch.bfloat16: 1, torch.float32: 2}
+
+
+def scatter_add_rows(dst2d, src2d, indices):
+    """dst2d[indices[i]] += src2d[i] in place (unique indices, negative = skip): fa_scatter_add_rows."""
+    _check(dst2d.is_cuda and dst2d.dim() == 2 and dst2d.is_contiguous() and src2d.is_contiguous() and src2d.dtype == dst2d.dtype
+           and src2d.shape[1] == dst2d.shape[1] and dst2d.dtype in _KIND, "bad scatter_add input")
+    _check(indices.dtype == torch.int64 and indices.is_contiguous(), "indices must be contiguous int64")
+    with _DeviceGuard(dst2d.device) as guard:
+        rc = _lib.fa_scatter_add_rows(_ptr(dst2d), _ptr(src2d), _ptr(indices), indices.numel(), dst2d.shape[1] * dst2d.element_size(),
+                                      _KIND[dst2d.dtype], guard.raw_stream())
+    _raise_if_failed(rc, "fa_scatter_add_rows")
+    return dst2d
+
+
+def varlen_index(mask):
+    """(b, s) bool CUDA mask -> indices (b*s,) int64 padded with -1, cu_seqlens (b+1,) int32, stats (2,) int32
+    [longest sequence, number of valid tokens] -- all device tensors, no host synchronisation (fa_varlen_index)."""
+    _check(mask.is_cuda and mask.dim() == 2, "mask must be a 2-D CUDA tensor")
+    m = (mask if mask.dtype == torch.bool else mask != 0).contiguous().view(torch.uint8)
+    b, s = m.shape
+    indices = torch.empty(b * s, dtype=torch.int64, device=mask.device)
+    cu = torch.empty(b + 1, dtype=torch.int32, device=mask.device)
+    stats = torch.empty(2, dtype=torch.int32, device=mask.device)
+    with _DeviceGuard(mask.device) as guard:
+        rc = _lib.fa_varlen_index(_ptr(m), b, s, _ptr(indices), _ptr(cu), _ptr(stats), guard.raw_stream())
+    _raise_if_failed(rc, "fa_varlen_index")
+    return indices, cu, stats
 
 
 def merge_partials(o_acc, lse_acc, o_blk, lse_blk, batch, seqlen, first, batch_rows=None):

@@ -161,12 +161,26 @@ int fa_bwd_block(const fa_params* p, void* stream);
 int fa_bwd_static_scratch(const fa_params* p, void* stream);
 
 /* Varlen pack / unpack (bert_padding.py).  Rows are `row_bytes` long (multiple of 4 bytes).
- * gather : dst[i, :] = src[indices[i], :]             for i in [0, n_indices)
- * scatter: dst[indices[i], :] = src[i, :]             (dst rows not named by indices are left untouched)
+ * gather : dst[i, :] = src[indices[i], :]             for i in [0, n_indices); a negative index gives a zero row
+ * scatter: dst[indices[i], :] = src[i, :]             (dst rows not named by indices are left untouched; negative = skip)
  * indices are int64 (torch.nonzero output). */
 int fa_gather_rows(void* dst, const void* src, const int64_t* indices, int64_t n_indices, int64_t row_bytes,
                    void* stream);
 int fa_scatter_rows(void* dst, const void* src, const int64_t* indices, int64_t n_indices, int64_t row_bytes,
+                    void* stream);
+
+/* dst[indices[i], :] += src[i, :] (indices unique; negative entries are skipped) -- the backward of
+ * index_first_axis_residual (flash_attn/bert_padding.py:67-96, `grad_residual.index_add(0, indices, grad_output)`).
+ * kind: 0 = fp16, 1 = bf16, 2 = fp32; rows a multiple of 16 bytes, 16-byte aligned. */
+int fa_scatter_add_rows(void* dst, const void* src, const int64_t* indices, int64_t n_indices, int64_t row_bytes,
+                        int32_t kind, void* stream);
+
+/* Varlen bookkeeping on the device, no host round trip (the reference's unpad_input does nonzero() and .item():
+ * flash_attn/bert_padding.py:99-119).  mask: (b, s) bytes, nonzero = valid token.  Outputs:
+ *   indices     (b * s) int64: flat positions of the valid tokens in order, then -1 up to the end (fa_gather_rows turns a
+ *               -1 into a zero row, fa_scatter_rows / fa_scatter_add_rows skip it);
+ *   cu_seqlens  (b + 1) int32;   stats[0] = longest sequence, stats[1] = number of valid tokens. */
+int fa_varlen_index(const uint8_t* mask, int32_t b, int32_t s, int64_t* indices, int32_t* cu_seqlens, int32_t* stats,
                     void* stream);
 
 /* Merge of two partial attention results over the same queries (K/V split across ring steps / GPUs): the reference's

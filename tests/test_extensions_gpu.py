@@ -316,3 +316,85 @@ def test_reference_blocksparse_interface_runs_unmodified_on_the_shim(dropout_p):
     (gpt,) = torch.autograd.grad(pt, qkv_p, g)
     assert orc.max_abs_err(U.unpack_rows(out_u, idx, b, s), ref) <= 2 * orc.max_abs_err(pt, ref) + 1e-6
     assert orc.max_abs_err(U.unpack_rows(dqkv_u, idx, b, s), gref) <= 2 * orc.max_abs_err(gpt, gref) + 1e-6
+
+
+# ------------------------------------------------------------------------------------------------------------
+# varlen bookkeeping on the device
+# ------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("b,s", [(1, 7), (3, 257), (16, 512), (33, 1000), (1500, 40), (4, 4096)])
+def test_unpad_input_nosync_matches_unpad_input(b, s):
+    """indices / cu_seqlens / packed rows equal the reference-style unpad_input (integer work: bit-exact), including
+    empty and full rows and more sequences than one scan chunk; entries past the total are -1 / zero rows."""
+    from flash_attn.bert_padding import pad_input, unpad_input, unpad_input_nosync
+    g = torch.Generator(device=DEV).manual_seed(b * 7919 + s)
+    lens = torch.randint(0, s + 1, (b,), device=DEV, generator=g)
+    lens[0] = s                      # a full row
+    if b > 2:
+        lens[1] = 0                  # an empty row
+    mask = torch.arange(s, device=DEV)[None] < lens[:, None]
+    if b > 3:                        # and one row with holes (a mask need not be a prefix)
+        mask[3] = torch.rand(s, device=DEV, generator=g) < 0.5
+    x = torch.randn(b, s, 24, device=DEV, dtype=torch.float16, generator=g)
+    xu, idx, cu, mx = unpad_input(x, mask)
+    xn, idxn, cun, mxn = unpad_input_nosync(x, mask)
+    nnz = idx.numel()
+    assert idxn.shape == (b * s,) and torch.equal(idxn[:nnz], idx) and bool((idxn[nnz:] == -1).all())
+    assert torch.equal(cun, cu) and mxn == s and mx <= mxn
+    assert torch.equal(xn[:nnz], xu) and xn[nnz:].abs().max().item() == 0 if nnz < b * s else torch.equal(xn, xu)
+    assert torch.equal(pad_input(xn, idxn, b, s), pad_input(xu, idx, b, s))
+    import flash_attn_cuda
+    _, _, stats = flash_attn_cuda.varlen_index(mask)
+    assert stats.tolist() == [int(mask.sum(-1).max()), nnz]
+
+
+def test_flash_attention_module_makes_no_host_synchronisation():
+    """FlashAttention.forward with a key_padding_mask, forward and backward, under torch's sync debug mode: the
+    reference synchronises twice per call in unpad_input (bert_padding.py:109-112); this path must not at all."""
+    from flash_attn.flash_attention import FlashAttention
+    b, s, h, d = 4, 300, 4, 64
+    torch.manual_seed(0)
+    qkv = torch.randn(b, s, 3, h, d, device=DEV, dtype=torch.float16, requires_grad=True)
+    mask = orc.generate_random_padding_mask(s, b, DEV, mode="third")
+    mod = FlashAttention().eval()
+    g = torch.randn(b, s, h, d, device=DEV, dtype=torch.float16)
+    out, _ = mod(qkv, key_padding_mask=mask, causal=True)          # warm-up: allocator, one-time kernel attributes
+    torch.autograd.grad(out, qkv, g)
+    torch.cuda.synchronize()
+    torch.cuda.set_sync_debug_mode("error")
+    try:
+        out, _ = mod(qkv, key_padding_mask=mask, causal=True)
+        (dqkv,) = torch.autograd.grad(out, qkv, g)
+    finally:
+        torch.cuda.set_sync_debug_mode("default")
+    xf = qkv.detach().float().requires_grad_()
+    ref, _ = orc.attention_qkvpacked_ref(xf, mask, causal=True)
+    (gref,) = torch.autograd.grad(ref, xf, g.float())
+    xp = qkv.detach().clone().requires_grad_()
+    pt, _ = orc.attention_qkvpacked_ref(xp, mask, causal=True, upcast=False, reorder_ops=True)
+    (gpt,) = torch.autograd.grad(pt, xp, g)
+    assert orc.within_2x(out, ref, pt)
+    valid = mask[:, :, None, None, None]
+    assert orc.max_abs_err(dqkv * valid, gref * valid) <= 2 * orc.max_abs_err(gpt * valid, gref * valid) + 1e-6
+    assert dqkv[~mask].abs().max().item() == 0           # padded tokens get exactly zero gradient
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16, torch.float32])
+def test_index_first_axis_residual_backward_kernel(dtype):
+    """forward (x[indices], x) / backward grad_residual + scatter(grad_output) (reference bert_padding.py:67-96),
+    through fa_scatter_add_rows; indices unique, so the result equals index_add bit for bit."""
+    from flash_attn.bert_padding import index_first_axis_residual
+    n, w = 3000, 96
+    g = torch.Generator(device=DEV).manual_seed(1)
+    x = torch.randn(n, 4, w // 4, device=DEV, dtype=dtype, generator=g, requires_grad=True)
+    idx = torch.randperm(n, device=DEV, generator=g)[:1234].sort().values
+    y, res = index_first_axis_residual(x, idx)
+    assert torch.equal(y, x[idx]) and torch.equal(res, x.detach())
+    gy, gres = torch.randn_like(y), torch.randn_like(res)
+    from flash_attn.bert_padding import IndexFirstAxisResidual
+
+    class _Ctx:
+        saved_tensors = (idx,)
+        first_axis_dim = n
+    got, _ = IndexFirstAxisResidual.backward(_Ctx, gy, gres)
+    want = gres.reshape(n, -1).index_add(0, idx, gy.reshape(idx.numel(), -1)).reshape(x.shape)
+    assert torch.equal(got, want)
