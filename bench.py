@@ -394,6 +394,14 @@ def run_ours(args, w):
     fwd_ms = sum(e[0].elapsed_time(e[1]) for e in ev) / args.steps
     bwd_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / args.steps
 
+    if args.profile:
+        if rank == 0:
+            print(json.dumps({"profile_run": True, "ms_per_step": ms_total / args.steps, "fwd_kernel_ms": kt["fwd_ms"] / max(kt["fwd_launches"], 1),
+                              "bwd_kernel_ms": kt["bwd_ms"] / max(kt["bwd_launches"], 1)}), flush=True)
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
     # ---- end-to-end: host buffers in, host buffers out, copies inside the timed region ----
     # The (batch x heads) units are independent, so the user-level call sequence splits the batch into chunks and
     # overlaps the pinned-memory H2D copy of chunk i+1 and the D2H copy of chunk i-1 with the kernels of chunk i
@@ -717,6 +725,8 @@ def main():
     ap.add_argument("--workload", default="d128", choices=sorted(WORKLOADS))
     ap.add_argument("--sweep", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile", action="store_true", help="runs under ncu: the headline steps only (no e2e / ring / sub-records / CPU legs; "
+                                                           "the line it prints is not a bench value)")
     ap.add_argument("--fwd-only", action="store_true", help="sweep: time the forward only")
     ap.add_argument("--max-seqlen", type=int, default=16384, help="sweep: largest seqlen")
     args = ap.parse_args()

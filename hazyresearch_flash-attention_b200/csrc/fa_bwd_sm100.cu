@@ -5,10 +5,12 @@
 //     P = exp(scale*S - lse)   dV = (P o Z / keep)^T dO   dP = (dO V^T) o Z / keep   dS = P o (dP - D)
 //     D = rowsum(dO o O)       dQ = scale * dS K          dK = scale * dS^T Q
 //
-// Two launches:  preprocess (D, -lse*log2e, per row)  ->  main.  The fp32 dQ accumulator is converted to 16 bit inside the
-// main kernel by whichever CTA of a (batch, head) pair finishes last (one counter per pair, bumped once per CTA); that CTA
-// also writes zeros back, so the accumulator is clean for the next call and needs neither a memset nor a postprocess pass.
-// (The blocksparse variant, whose contributor count per tile depends on the mask, keeps the separate postprocess launch.)
+// Three launches:  preprocess (D, -lse*log2e, per row)  ->  main  ->  postprocess (dQ fp32 accumulator -> 16 bit, zeros written
+// back: the accumulator is clean for the next call, so a kept workspace never needs a memset).
+// Converting dQ INSIDE the main kernel (last CTA of a tile / of a (batch, head) pair, register- and TMA-based, four protocols)
+// was built and measured in round 2 and lost at every size, S = 512 included: the conversion's loads queue behind the other
+// SMs' dQ reductions, which saturate the L2 atomic path (~170 us per (batch, head) on the converting SM; 0.23 ms of a 2.35 ms
+// kernel against 0.10 - 0.16 ms as a separate HBM-speed pass).  Numbers: profiles/r02_dq_signal_ab.log.
 //
 // Main kernel: one CTA owns a block of 128 keys (K and V tiles stay in shared memory) and streams 128-row Q / dO tiles.
 // Everything the softmax-side threads touch is computed TRANSPOSED (keys on TMEM lanes, queries on TMEM columns):
@@ -58,20 +60,12 @@ struct BwdSmem {
   static constexpr int kMaskOff = kStatOff + kQStages * 1024;    // dropout keep bits: 2 x [4 key words][128 queries] u32
   static constexpr int kListOff = kMaskOff + 2 * 2048;    // blocksparse: int16 list[512], uint8 flags[512]
   static constexpr int kBarOff = kListOff + kMaxSparseTiles * 3;
-  static constexpr int kNumBars = 27;                     // + k_fix, q_fix, do_fix, fin_full[3], fin_empty[3]
-  // dQ finalisation at the end of a (batch, head)'s last CTA: ring of kFinStages accumulator tiles over the (then dead)
-  // K / V / Q / dO / dS buffers, a 16 KB block of zeros in the dQ staging area
-  static constexpr int kFinStages = 3;
-  static constexpr int kAccTile = 128 * DPAD * 4;         // one fp32 accumulator tile
-  static constexpr int kZeroBytes = 16384;
+  static constexpr int kNumBars = 21;                     // + k_fix, q_fix, do_fix
   static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
   static constexpr int kTotal = kTmemPtrOff + 16;
   static constexpr int kDynamicBytes = kTotal + 1024;     // + alignment slack
 };
 static_assert(BwdSmem<128>::kDynamicBytes <= 232448, "shared memory budget");
-static_assert(BwdSmem<128>::kFinStages * BwdSmem<128>::kAccTile <= BwdSmem<128>::kDqOff &&
-              BwdSmem<64>::kFinStages * BwdSmem<64>::kAccTile <= BwdSmem<64>::kDqOff, "finalisation ring overlaps the zero block");
-static_assert(BwdSmem<128>::kZeroBytes <= 4 * BwdSmem<128>::kDqBufs * 2048, "zero block must fit the dQ staging area");
 
 struct BwdTensorMaps {
   CUtensorMap q, k, v, dout;
@@ -83,8 +77,7 @@ struct BwdTensorMaps {
 struct BwdWs {
   float* nl;         // (h, n_slots * 128): -lse*log2e, -inf for rows that must produce P = 0
   float* dsum;       // (h, n_slots * 128): D = rowsum(dO o O), 0 for invalid rows
-  float* dq_accum;   // (h, n_slots, 4 row quarters, DPAD/4, 32, 4) fp32; all zero on entry and on exit
-  uint32_t* dq_count;   // (h, n_slots, 4): word 0 of a sequence's first slot counts its finished key-block CTAs; zero on entry and exit
+  float* dq_accum;   // (h, n_slots, 4 row quarters, DPAD/4, 32, 4) fp32; all zero on entry, and again after the postprocess pass
   int n_slots;
 };
 __device__ __forceinline__ int tile_slot(int q_begin, int bidb, int m) { return (q_begin >> 7) + bidb + m; }
@@ -219,7 +212,6 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
   int16_t* tile_list = reinterpret_cast<int16_t*>(smem + L::kListOff);
   uint8_t* tile_flags = smem + L::kListOff + kMaxSparseTiles * 2;
   __shared__ int s_num_active;
-  __shared__ uint32_t s_bh_last;
 
   // Q tiles this CTA visits
   const int n_qt_total = (seq.seqlen_q + kBM - 1) / kBM;
@@ -263,7 +255,6 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
   const bool kv_partial = k_valid < kBN;
   const int q_valid_last = seq.seqlen_q - (n_qt_total - 1) * kBM;   // valid rows of the last query tile (1..128)
   const bool q_partial = n_iter > 0 && q_valid_last < kBM && tile_of(n_iter - 1) == n_qt_total - 1;   // then it is the last iteration
-  constexpr bool kFusedDq = !kSparse;                    // dQ finalised in-kernel (see the end of the kernel)
   const int slot0 = tile_slot(seq.q_begin, bidb, 0);
 
   uint8_t* sK = smem + L::kKOff;
@@ -336,14 +327,6 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
   if (threadIdx.x == 0) FA_CTA_MARK(3, clock64());
-  // the dQ tiles of this (batch, head) are complete when every key-block CTA of the sequence (the ones that did not
-  // return above: n_blk < nkb_seq) has added its partials -- see the end of the kernel
-  const int nkb_seq = (seq.seqlen_k + kBN - 1) / kBN;
-  auto dq_row_ptr = [&](int row) -> uint16_t* {   // row within the sequence
-    return row < seq.seqlen_q ? reinterpret_cast<uint16_t*>(p.dq) + (int64_t)(seq.q_begin + row) * p.dq_row_stride + (int64_t)bidh * p.dq_head_stride
-                              : nullptr;
-  };
-
   uint8_t* sDs = smem + L::kDsOff;
   uint8_t* sDq = smem + L::kDqOff;
   uint32_t* sMask = reinterpret_cast<uint32_t*>(smem + L::kMaskOff);
@@ -622,32 +605,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
       if (wq == 0) FA_TRACE(18);
     }
     if (warp == 8 && lane == 0) FA_CTA_MARK(9, clock64());    // last chunk issued
-    if constexpr (kFusedDq) {
-      // The CTA's contribution counts once its reductions have COMPLETED (wait_group without .read: the sums are in L2).
-      // The four drain warps meet on a named barrier and warp 8 bumps the (batch, head) counter right here, so that the
-      // completion wait, the fence and the atomic's round trip (2-3 us together) run under the dK / dV epilogue of the
-      // compute warps instead of after it; the verdict reaches the other warps through the CTA-wide barrier at the end.
-      if (lane == 0) bulk_wait_group<0>();
-      __syncwarp();
-      named_bar_sync(4, 128);
-      if (warp == 8 && lane == 0) {
-        uint32_t* cnt = ws.dq_count + ((int64_t)bidh * ws.n_slots + slot0) * 4;
-        __threadfence();
-        const uint32_t old = atomicAdd(cnt, 1u);
-        const bool last = old + 1 == static_cast<uint32_t>(nkb_seq);
-        if (last) {
-          *cnt = 0;                       // clean for the next call
-          for (int st = 0; st < L::kFinStages; ++st) {
-            mbar_init(&bars[21 + st], 1);                    // fin_full
-            mbar_init(&bars[24 + st], kBwdThreads / 32);     // fin_empty
-          }
-          fence_mbar_init();
-        }
-        s_bh_last = last ? 1 : 0;
-      }
-    } else {
-      if (lane == 0) bulk_wait_group_read<0>();   // the staging buffers may go away; the reductions complete on their own
-    }
+    if (lane == 0) bulk_wait_group_read<0>();   // the staging buffers may go away; the reductions complete on their own
     if (warp == 8 && lane == 0) FA_CTA_MARK(10, clock64());
   } else {
     // ===================================== compute warps =======================================
@@ -869,80 +827,6 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
   }
-  if constexpr (kFusedDq) {
-    // dQ finalisation.  ONE counter per (batch, head), bumped once per CTA by the drain warps (see there) after their bulk
-    // reductions have completed; s_bh_last is their verdict.  The CTA that brings it to the number of key blocks owns the
-    // finished sums of every query tile of this (batch, head): it converts them (fp32 accumulator in L2 -> x scale ->
-    // 16-bit dq) and writes zeros back, which leaves accumulator and counter clean for the next call -- no memset, no
-    // postprocess launch.  (Per-tile counters were measured first: a fence + atomic per tile and drain warp sits on the
-    // dQ -> drain -> dP chain and cost 50 % of the kernel, profiles/r02_dq_signal_ab.log.)
-    uint64_t* fin_full = bars + 21;
-    uint64_t* fin_empty = bars + 24;
-    if (s_bh_last != 0 && n_qt_total > 0) {
-      // Every buffer of the CTA is dead now.  The accumulator tiles come in through bulk copies (a 3-deep ring, completion
-      // on mbarriers), all 16 warps convert out of shared memory, and the zeros go back as bulk stores from a zeroed
-      // 16 KB block -- no register-latency-bound loads, the copy engine runs at the SM's full L2 bandwidth.
-      constexpr int kChunks = DPAD / 16;
-      uint8_t* fbuf = smem;
-      uint8_t* zbuf = smem + L::kDqOff;
-      for (int i = threadIdx.x; i < L::kZeroBytes / 16; i += kBwdThreads) st_shared_v4(smem_u32(zbuf) + i * 16, 0u, 0u, 0u, 0u);
-      fence_proxy_async();
-      __syncthreads();
-      float* acc0 = ws.dq_accum + ((int64_t)bidh * ws.n_slots + slot0) * (kBM * DPAD);
-      const bool producer = threadIdx.x == 0;
-      if (producer) {
-        __threadfence();            // acquire side of the counter: the other CTAs' completed reductions ...
-        fence_proxy_async_all();    // ... before this thread's bulk copies read them
-        for (int st = 0; st < L::kFinStages && st < n_qt_total; ++st) {
-          mbar_arrive_expect_tx(&fin_full[st], L::kAccTile);
-          bulk_load_1d(fbuf + st * L::kAccTile, acc0 + (int64_t)st * (kBM * DPAD), L::kAccTile, &fin_full[st]);
-        }
-      }
-      const int q4 = warp & 3;
-      const float sc = p.softmax_scale;
-      for (int m = 0; m < n_qt_total; ++m) {
-        const int st = m % L::kFinStages;
-        mbar_wait(&fin_full[st], (m / L::kFinStages) & 1);
-        uint16_t* dq_row = dq_row_ptr(m * kBM + q4 * 32 + lane);
-        const uint32_t qbase = smem_u32(fbuf) + st * L::kAccTile + q4 * (32 * DPAD * 4) + lane * 16;
-#pragma unroll
-        for (int k = warp >> 2; k < kChunks; k += 4) {   // quarter layout: [chunk (16 columns)][4 column groups][32 rows][4]
-          const float4 v0 = lds128(qbase + k * 2048), v1 = lds128(qbase + k * 2048 + 512);
-          const float4 v2 = lds128(qbase + k * 2048 + 1024), v3 = lds128(qbase + k * 2048 + 1536);
-          uint4 lo, hi;
-          lo.x = pack2<kBf16>(v0.x * sc, v0.y * sc);
-          lo.y = pack2<kBf16>(v0.z * sc, v0.w * sc);
-          lo.z = pack2<kBf16>(v1.x * sc, v1.y * sc);
-          lo.w = pack2<kBf16>(v1.z * sc, v1.w * sc);
-          hi.x = pack2<kBf16>(v2.x * sc, v2.y * sc);
-          hi.y = pack2<kBf16>(v2.z * sc, v2.w * sc);
-          hi.z = pack2<kBf16>(v3.x * sc, v3.y * sc);
-          hi.w = pack2<kBf16>(v3.z * sc, v3.w * sc);
-          const int col = k * 16;
-          if (dq_row != nullptr && col < p.d) *reinterpret_cast<uint4*>(dq_row + col) = lo;
-          if (dq_row != nullptr && col + 8 < p.d) *reinterpret_cast<uint4*>(dq_row + col + 8) = hi;
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&fin_empty[st]);
-        if (producer) {
-          // tile m has landed (fin_full observed): its zeros can go back right away
-          float* acc_m = acc0 + (int64_t)m * (kBM * DPAD);
-#pragma unroll
-          for (int z = 0; z < L::kAccTile / L::kZeroBytes; ++z)
-            bulk_store_1d(reinterpret_cast<uint8_t*>(acc_m) + z * L::kZeroBytes, zbuf, L::kZeroBytes);
-          bulk_commit_group();
-          // refill the stage tile m-1 used, one iteration late: by now every warp has long arrived on its barrier
-          if (m >= 1 && m - 1 + L::kFinStages < n_qt_total) {
-            const int sp = (m - 1) % L::kFinStages;
-            mbar_wait(&fin_empty[sp], ((m - 1) / L::kFinStages) & 1);
-            mbar_arrive_expect_tx(&fin_full[sp], L::kAccTile);
-            bulk_load_1d(fbuf + sp * L::kAccTile, acc0 + (int64_t)(m - 1 + L::kFinStages) * (kBM * DPAD), L::kAccTile, &fin_full[sp]);
-          }
-        }
-      }
-      if (producer) bulk_wait_group_read<0>();   // the zero block is read by stores still in flight
-    }
-  }
 #ifdef FA_BWD_TRACE
   if (threadIdx.x == 0) {
     FA_CTA_MARK(5, clock64());
@@ -1012,7 +896,7 @@ __global__ void __launch_bounds__(256) bwd_preprocess_kernel(const fa_params p, 
 }
 
 // ------------------------------------------------------------------------------------------------
-// postprocess (blocksparse variant only): dq = scale * dq_accum -> 16 bit, caller's strides; zeros written back
+// postprocess: dq = scale * dq_accum -> 16 bit, caller's strides; zeros written back (accumulator clean for the next call)
 // ------------------------------------------------------------------------------------------------
 template <bool kBf16, int DPAD>
 __global__ void __launch_bounds__(128) bwd_postprocess_kernel(const fa_params p, const BwdWs ws, const int n_qtiles) {
@@ -1034,7 +918,7 @@ __global__ void __launch_bounds__(128) bwd_postprocess_kernel(const fa_params p,
 inline uint64_t align256(uint64_t x) { return (x + 255) & ~uint64_t(255); }
 
 struct BwdWsLayout {
-  uint64_t nl_off, dsum_off, accum_off, count_off, total;
+  uint64_t nl_off, dsum_off, accum_off, total;
   int n_slots, dpad;
 };
 
@@ -1044,8 +928,7 @@ BwdWsLayout bwd_ws_layout(const fa_params& p) {
   l.dpad = p.d <= 64 ? 64 : 128;
   const uint64_t rows = (uint64_t)p.h * l.n_slots * kBM;
   l.accum_off = 0;                                         // [0, nl_off): the "zero on entry / zero on exit" region
-  l.count_off = align256(rows * l.dpad * 4);
-  l.nl_off = l.count_off + align256((uint64_t)p.h * l.n_slots * 4 * 4);
+  l.nl_off = align256(rows * l.dpad * 4);
   l.dsum_off = l.nl_off + align256(rows * 4);
   l.total = l.dsum_off + align256(rows * 4);
   return l;
@@ -1129,7 +1012,6 @@ cudaError_t launch_bwd_sm100(const fa_params& p, const BlockMaskView& bm, void* 
   ws.nl = reinterpret_cast<float*>(base + l.nl_off);
   ws.dsum = reinterpret_cast<float*>(base + l.dsum_off);
   ws.dq_accum = reinterpret_cast<float*>(base + l.accum_off);
-  ws.dq_count = reinterpret_cast<uint32_t*>(base + l.count_off);
   ws.n_slots = l.n_slots;
   cudaError_t e;
   if (!(p.flags & FA_FLAG_WS_ZEROED)) {
@@ -1173,7 +1055,7 @@ cudaError_t launch_bwd_sm100(const fa_params& p, const BlockMaskView& bm, void* 
 #endif
     if (e != cudaSuccess) return e;
   }
-  if (bm.dense != nullptr && n_qtiles > 0 && p.total_q > 0) {
+  if (n_qtiles > 0 && p.total_q > 0) {
     const dim3 grid(static_cast<unsigned>(n_qtiles * p.b), p.h, 1);
     if (l.dpad == 64) {
       if (p.is_bf16) bwd_postprocess_kernel<true, 64><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
