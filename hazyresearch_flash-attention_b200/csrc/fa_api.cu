@@ -80,7 +80,7 @@ int validate_common(const fa_params* p, bool bwd, bool block) {
       {p->v, p->v_row_stride, p->v_head_stride, "v", true},
       {p->o, p->o_row_stride, p->o_head_stride, "o", true},
       {p->dout, p->do_row_stride, p->do_head_stride, "dout", bwd},
-      {p->dq, p->dq_row_stride, p->dq_head_stride, "dq", bwd},
+      {p->dq, p->dq_row_stride, p->dq_head_stride, "dq", bwd && !(p->flags & FA_FLAG_KEEP_DQ_ACCUM)},
       {p->dk, p->dk_row_stride, p->dk_head_stride, "dk", bwd},
       {p->dv, p->dv_row_stride, p->dv_head_stride, "dv", bwd},
   };
@@ -95,7 +95,12 @@ int validate_common(const fa_params* p, bool bwd, bool block) {
                   t.name, (long long)t.rs, (long long)t.hs);
   }
   if (bwd && p->softmax_d == nullptr) return fail(FA_ERR_INVALID_ARGUMENT, "softmax_d is NULL");
-  if (p->flags & ~(FA_FLAG_WS_ZEROED)) return fail(FA_ERR_INVALID_ARGUMENT, "unknown flags 0x%x", p->flags);
+  if (p->flags & ~(FA_FLAG_WS_ZEROED | FA_FLAG_KEEP_DQ_ACCUM)) return fail(FA_ERR_INVALID_ARGUMENT, "unknown flags 0x%x", p->flags);
+  if ((p->flags & FA_FLAG_KEEP_DQ_ACCUM) && (!bwd || block || p->impl == FA_IMPL_SIMT))
+    return fail(FA_ERR_INVALID_ARGUMENT, "FA_FLAG_KEEP_DQ_ACCUM applies to fa_bwd with the tcgen05 kernels only");
+  if ((p->flags & FA_FLAG_KEEP_DQ_ACCUM) && !(p->flags & FA_FLAG_WS_ZEROED))
+    return fail(FA_ERR_INVALID_ARGUMENT, "FA_FLAG_KEEP_DQ_ACCUM needs FA_FLAG_WS_ZEROED: the caller owns the workspace and clears it once "
+                                         "(without the flag the library would clear the running sum on every call)");
   if (p->alibi_slopes != nullptr && block)
     return fail(FA_ERR_INVALID_ARGUMENT, "blocksparse attention does not take an attention bias");
   if (p->impl == FA_IMPL_SIMT && (p->b > 65535 || p->h > 65535))
@@ -671,6 +676,24 @@ int fa_bwd_static_scratch(const fa_params* p, void* stream) {
   // `stream`, the range that has to start at zero (cudaMemsetAsync -- not an allocation)
   q.flags &= ~static_cast<uint32_t>(FA_FLAG_WS_ZEROED);
   return fa::run_bwd(&q, stream, false);
+}
+
+int fa_bwd_dq_finalize(const fa_params* p, void* stream) {
+  fa::g_last_error[0] = 0;
+  if (p == nullptr) return fa::fail(FA_ERR_INVALID_ARGUMENT, "params is NULL");
+  if (p->b <= 0 || p->h <= 0 || p->d <= 0 || p->d % 8 != 0 || p->d > 128 || p->total_q < 0 || p->max_seqlen_q < 0)
+    return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_bwd_dq_finalize: bad sizes");
+  if (p->cu_seqlens_q == nullptr || p->cu_seqlens_k == nullptr) return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_bwd_dq_finalize: cu_seqlens are NULL");
+  if (p->total_q > 0 && (p->dq == nullptr || !fa::aligned16(p->dq) || p->dq_row_stride % 8 != 0 || p->dq_head_stride % 8 != 0))
+    return fa::fail(FA_ERR_INVALID_ARGUMENT, "fa_bwd_dq_finalize: dq must be non-NULL, 16-byte aligned, strides multiples of 8");
+  int rc = fa::check_device();
+  if (rc != FA_OK) return rc;
+  const uint64_t need = fa::bwd_sm100_workspace_bytes(*p);
+  if (p->workspace == nullptr || p->workspace_bytes < need)
+    return fa::fail(FA_ERR_WORKSPACE, "workspace too small: need %llu bytes, have %llu", (unsigned long long)need,
+                    (unsigned long long)p->workspace_bytes);
+  cudaError_t e = fa::launch_bwd_dq_finalize(*p, p->workspace, static_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? FA_OK : fa::cuda_fail(e, "dq finalize launch");
 }
 
 int fa_fwd_block(const fa_params* p, void* stream) { return fa::run_fwd(p, stream, true); }

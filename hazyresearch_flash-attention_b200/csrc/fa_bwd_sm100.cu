@@ -877,7 +877,7 @@ __global__ void __launch_bounds__(256) bwd_preprocess_kernel(const fa_params p, 
     for (int t = 0; t < 8; ++t) acc = fmaf(Elem<kBf16>::to_float(oe[t]), Elem<kBf16>::to_float(ge[t]), acc);
 #pragma unroll
     for (int o = 8; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    if (valid && seq.seqlen_k <= 0 && part * 8 < p.d)
+    if (valid && seq.seqlen_k <= 0 && part * 8 < p.d && p.dq != nullptr)
       *reinterpret_cast<uint4*>(reinterpret_cast<T*>(p.dq) + (int64_t)(seq.q_begin + row) * p.dq_row_stride + (int64_t)bidh * p.dq_head_stride + part * 8) =
           make_uint4(0u, 0u, 0u, 0u);
     if (part == 0) {
@@ -1055,7 +1055,7 @@ cudaError_t launch_bwd_sm100(const fa_params& p, const BlockMaskView& bm, void* 
 #endif
     if (e != cudaSuccess) return e;
   }
-  if (n_qtiles > 0 && p.total_q > 0) {
+  if (!(p.flags & FA_FLAG_KEEP_DQ_ACCUM) && n_qtiles > 0 && p.total_q > 0) {
     const dim3 grid(static_cast<unsigned>(n_qtiles * p.b), p.h, 1);
     if (l.dpad == 64) {
       if (p.is_bf16) bwd_postprocess_kernel<true, 64><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
@@ -1069,6 +1069,29 @@ cudaError_t launch_bwd_sm100(const fa_params& p, const BlockMaskView& bm, void* 
     if (e != cudaSuccess) return e;
   }
   return cudaSuccess;
+}
+
+cudaError_t launch_bwd_dq_finalize(const fa_params& p, void* workspace, cudaStream_t stream) {
+  const BwdWsLayout l = bwd_ws_layout(p);
+  const int n_qtiles = (p.max_seqlen_q + kBM - 1) / kBM;
+  if (n_qtiles <= 0 || p.total_q <= 0) return cudaSuccess;
+  if ((int64_t)n_qtiles * p.b > 0x7fffffffLL || p.h > 65535) return cudaErrorInvalidConfiguration;
+  BwdWs ws;
+  uint8_t* base = static_cast<uint8_t*>(workspace);
+  ws.nl = reinterpret_cast<float*>(base + l.nl_off);
+  ws.dsum = reinterpret_cast<float*>(base + l.dsum_off);
+  ws.dq_accum = reinterpret_cast<float*>(base + l.accum_off);
+  ws.n_slots = l.n_slots;
+  const dim3 grid(static_cast<unsigned>(n_qtiles * p.b), p.h, 1);
+  if (l.dpad == 64) {
+    if (p.is_bf16) bwd_postprocess_kernel<true, 64><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
+    else bwd_postprocess_kernel<false, 64><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
+  } else {
+    if (p.is_bf16) bwd_postprocess_kernel<true, 128><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
+    else bwd_postprocess_kernel<false, 128><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
+  }
+  count_launch();
+  return cudaGetLastError();
 }
 
 }  // namespace fa

@@ -28,6 +28,8 @@ cudaError_t launch_bwd_sm100(const fa_params& p, const BlockMaskView& bm, void* 
 // (d, h, total) TMA view of a packed (total, h, d) 16-bit tensor: box 64 x 1 x box_rows, 128-byte swizzle (fa_fwd_sm100.cu)
 bool make_tensor_map_3d(CUtensorMap* map, const void* base, int d, int h, int64_t total, int64_t row_stride,
                         int64_t head_stride, int box_rows);
+// only the dQ conversion pass of the backward (after FA_FLAG_KEEP_DQ_ACCUM calls)
+cudaError_t launch_bwd_dq_finalize(const fa_params& p, void* workspace, cudaStream_t stream);
 uint64_t bwd_sm100_workspace_bytes(const fa_params& p);
 uint64_t bwd_sm100_workspace_zero_bytes(const fa_params& p);   // the scratch starts with this many zero-on-entry / zero-on-exit bytes
 

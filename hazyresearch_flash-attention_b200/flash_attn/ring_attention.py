@@ -85,28 +85,47 @@ class CudaBlockOps:
                                       seqused_q=half if q_len == 1 else None, seqused_k=half if k_len == 1 else None)
         return o, lse
 
-    def bwd(self, dout, q, k, v, out, lse, b, c, plan, scale):
-        """lse: the FINAL (b, h, 2c) log-sum-exp.  -> dq_blk (rows from q_off*c on), dk_blk, dv_blk ((b*2c) rows, the
-        first k_len*c of every batch element written)"""
+    def dq_begin(self, q, b, c):
+        """dQ of a whole ring pass accumulates in fp32 INSIDE the backward's own workspace (FA_FLAG_KEEP_DQ_ACCUM): every step
+        adds its partial sums to the same tile slots, one conversion pass at the end -- no per-step 16-bit dQ block, no
+        separate accumulate pass.  -> state for bwd() / dq_end()."""
+        cu, _ = self._index(b, c, q.device)
+        ws = torch.zeros(self.lib.bwd_workspace_bytes(q, cu, 2 * c), dtype=torch.uint8, device=q.device)
+        return ws
+
+    def bwd(self, dout, q, k, v, out, lse, b, c, plan, scale, dq_state):
+        """lse: the FINAL (b, h, 2c) log-sum-exp.  dQ is added into dq_state; -> dkv_blk (2, b*2c, h, d) 16 bit, the first
+        k_len*c rows of every batch element written.  The query sub-range is addressed through cu_seqlens_q (+ q_off*c) on
+        the UNSHIFTED tensors, so that every step maps its query tiles to the same accumulator slots."""
         q_off, q_len, k_len, causal = plan
         cu, half = self._index(b, c, q.device)
-        qv = q[q_off * c:]
-        dq, dk, dv = torch.empty_like(qv), torch.empty_like(k), torch.empty_like(v)
+        cu_q = cu if q_off == 0 else self._shifted(cu, q_off * c)
+        dkv = torch.empty((2,) + tuple(k.shape), dtype=k.dtype, device=k.device)
         lse_v = lse if q_len == 2 else lse[:, :, q_off * c:(q_off + q_len) * c].contiguous()
-        self.lib.bwd(dout[q_off * c:], qv, k, v, out[q_off * c:], lse_v, dq, dk, dv, cu, cu, q_len * c, k_len * c, 0.0,
-                     scale, False, causal, None, seqused_q=half if q_len == 1 else None,
-                     seqused_k=half if k_len == 1 else None)
-        return dq, dk, dv
+        self.lib.bwd(dout, q, k, v, out, lse_v, None, dkv[0], dkv[1], cu_q, cu, q_len * c, k_len * c, 0.0, scale, False, causal,
+                     None, seqused_q=half if q_len == 1 else None, seqused_k=half if k_len == 1 else None, dq_workspace=dq_state)
+        return dkv
+
+    def dq_end(self, dq_state, q, b, c, scale):
+        cu, _ = self._index(b, c, q.device)
+        return self.lib.bwd_dq_finalize(torch.empty_like(q), cu, 2 * c, scale, dq_state)
+
+    def _shifted(self, cu, off):
+        key = ("shift", cu.data_ptr(), off)
+        if key not in self._cache:
+            self._cache[key] = cu + off
+        return self._cache[key]
 
     def merge(self, o_acc, lse_acc, o_blk, lse_blk, b, c, plan, first):
         q_off, q_len = plan[0], plan[1]
         self.lib.merge_partials(o_acc[q_off * c:], lse_acc[:, :, q_off * c:], o_blk, lse_blk, b, q_len * c, first,
                                 batch_rows=2 * c)
 
-    def accumulate(self, dst, src, b, c, off, length):
-        """dst fp32 (b*2c, h, d) rows [off*c, (off+length)*c) of every batch element += src (rows from off*c on)"""
-        row = dst.shape[1] * dst.shape[2]
-        self.lib.accumulate_f32(dst[off * c:], src, b, length * c * row, 2 * c * row, 2 * c * row)
+    def accumulate_dkv(self, acc, dkv_blk, b, c, k_len):
+        """acc fp32 (2, b*2c, h, d) += dkv_blk (same shape, 16 bit) on the first k_len*c rows of every batch element of both
+        halves: one launch ((dK, dV) x batch = 2b runs of k_len*c rows)"""
+        row = acc.shape[2] * acc.shape[3]
+        self.lib.accumulate_f32(acc, dkv_blk, 2 * b, k_len * c * row, 2 * c * row, 2 * c * row)
 
 
 _default_ops = None
@@ -436,33 +455,31 @@ def ring_backward(dout, q, k, v, out, lse, softmax_scale, group=None, ops=None, 
     b, two, c, h, d = q.shape
     rows = b * 2 * c
     qf, of, gf = (t.reshape(rows, h, d) for t in (q, out, dout.contiguous()))
-    dq_acc = torch.zeros(rows, h, d, dtype=torch.float32, device=q.device)
     tr = _make_transport(ring, q, rows, transport)
     kvs = tr.kv_stream(k.reshape(rows, h, d), v.reshape(rows, h, d))
     acc = tr.dkv_stream(rows, h, d, q.device)       # follows its K/V block around the ring, one step behind
+    dq_state = ops.dq_begin(qf, b, c)               # dQ stays local and accumulates in fp32 over all steps
     for step in range(ring.world):
         more = step + 1 < ring.world
         if more:
             kvs.prefetch(step)
         plan = _step_plan(step, ring.rank, ring.world)
-        q_off, q_len, k_len, _ = plan
         with _span("bwd_kernels", step):
-            dq_blk, dk_blk, dv_blk = ops.bwd(gf, qf, kvs.k, kvs.v, of, lse, b, c, plan, softmax_scale)
-            ops.accumulate(dq_acc, dq_blk, b, c, q_off, q_len)
+            dkv_blk = ops.bwd(gf, qf, kvs.k, kvs.v, of, lse, b, c, plan, softmax_scale, dq_state)
         if step > 0:                    # the accumulator of the block held now left the previous rank a step ago
             with _span("bwd_wait_dkv", step):
                 acc.arrive()
         with _span("bwd_accumulate", step):
-            ops.accumulate(acc.cur[0], dk_blk, b, c, 0, k_len)
-            ops.accumulate(acc.cur[1], dv_blk, b, c, 0, k_len)
+            ops.accumulate_dkv(acc.cur, dkv_blk, b, c, plan[2])
         acc.depart(step)                # travels under the next step's kernel; after the last step it goes home
         if more:
             with _span("bwd_wait_kv", step):
                 kvs.advance()
+    dq = ops.dq_end(dq_state, qf, b, c, softmax_scale)
     with _span("bwd_wait_dkv", ring.world):
         dkv = acc.home()
     shape = (b, 2, c, h, d)
-    return dq_acc.to(q.dtype).reshape(shape), dkv[0].to(q.dtype).reshape(shape), dkv[1].to(q.dtype).reshape(shape)
+    return dq.reshape(shape), dkv[0].to(q.dtype).reshape(shape), dkv[1].to(q.dtype).reshape(shape)
 
 
 class RingFlashAttnFunc(torch.autograd.Function):

@@ -19,7 +19,7 @@ _LIB_PATH = os.environ.get("FA_B200_LIB") or os.path.join(_HERE, "csrc", "libfa_
 FA_IMPL_AUTO, FA_IMPL_TCGEN05, FA_IMPL_SIMT = 0, 1, 2
 FA_OP_FWD, FA_OP_BWD, FA_OP_FWD_BLOCK, FA_OP_BWD_BLOCK = 0, 1, 2, 3
 
-FA_FLAG_WS_ZEROED = 1
+FA_FLAG_WS_ZEROED, FA_FLAG_KEEP_DQ_ACCUM = 1, 2
 
 # fa_params.impl of every call.  Always FA_IMPL_AUTO (the tcgen05 kernels) in the product; the GPU test-suite patches
 # this module attribute to FA_IMPL_SIMT to cross-check against the library's CUDA-core kernels (tests/fa_test_utils.py).
@@ -59,7 +59,7 @@ def _load_library():
     lib.fa_workspace_bytes.argtypes = [ctypes.POINTER(FaParams), ctypes.c_int]
     lib.fa_philox_increment.restype = ctypes.c_uint64
     lib.fa_philox_increment.argtypes = [ctypes.POINTER(FaParams)]
-    for name in ("fa_fwd", "fa_bwd", "fa_fwd_block", "fa_bwd_block", "fa_bwd_static_scratch"):
+    for name in ("fa_fwd", "fa_bwd", "fa_fwd_block", "fa_bwd_block", "fa_bwd_static_scratch", "fa_bwd_dq_finalize"):
         fn = getattr(lib, name)
         fn.restype = ctypes.c_int
         fn.argtypes = [ctypes.POINTER(FaParams), ctypes.c_void_p]
@@ -374,9 +374,13 @@ def _fwd_impl(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, p
 
 def _bwd_impl(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seqlens_k, max_seqlen_q,
               max_seqlen_k, p_dropout, softmax_scale, zero_tensors, is_causal, gen, blockmask=None, seqused_q=None,
-              seqused_k=None, alibi_slopes=None):
+              seqused_k=None, alibi_slopes=None, dq_workspace=None):
     b, total_q, total_k, h, d = _check_qkv(q, k, v, cu_seqlens_q, cu_seqlens_k)
     dt, q_shape, k_shape = q.dtype, (total_q, h, d), (total_k, h, d)
+    if dq_workspace is not None:      # dQ stays in the caller's workspace (FA_FLAG_KEEP_DQ_ACCUM): no dq tensor is written
+        _check(dq is None and blockmask is None and not zero_tensors,
+               "dq_workspace: pass dq=None (bwd_dq_finalize produces it), no blockmask, zero_tensors=False")
+        dq = q                        # stands in for the shape / dtype checks below; its pointer is not handed to the library
     if not (dout.is_cuda and out.is_cuda and dq.is_cuda and dk.is_cuda and dv.is_cuda
             and dout.dtype is dt and out.dtype is dt and dq.dtype is dt and dk.dtype is dt and dv.dtype is dt
             and dout.shape == q_shape and out.shape == q_shape and dq.shape == q_shape
@@ -415,7 +419,15 @@ def _bwd_impl(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seql
             P.blockmask_ncol, P.blockmask_nrow = blockmask.shape
             op = FA_OP_BWD_BLOCK
         stream = guard.raw_stream()
-        ws = _workspace(P, op, q.device, stream)
+        if dq_workspace is not None:
+            nbytes = int(_lib.fa_workspace_bytes(ctypes.byref(P), op))
+            _check(dq_workspace.is_cuda and dq_workspace.dtype == torch.uint8 and dq_workspace.numel() >= nbytes,
+                   f"dq_workspace must be a uint8 CUDA tensor of at least {nbytes} bytes (bwd_workspace_bytes), zero-filled once")
+            P.workspace, P.workspace_bytes = dq_workspace.data_ptr(), dq_workspace.numel()
+            P.flags |= FA_FLAG_WS_ZEROED | FA_FLAG_KEEP_DQ_ACCUM
+            P.dq = None
+        else:
+            ws = _workspace(P, op, q.device, stream)
         _set_philox(P, _philox_state(p_dropout, gen, q.device, P, stream))
         fn = _lib.fa_bwd if blockmask is None else _lib.fa_bwd_block
         _raise_if_failed(fn(ctypes.byref(P), stream), "flash_attn_cuda.bwd")
@@ -449,12 +461,41 @@ def fwd_ex(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, p_dr
 
 def bwd(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k,
         p_dropout, softmax_scale, zero_tensors, is_causal, gen=None, seqused_q=None, seqused_k=None,
-        alibi_slopes=None):
+        alibi_slopes=None, dq_workspace=None):
     """Writes dq, dk, dv in place (any row/head stride) and returns softmax_d = rowsum(dO*O).
-    Call site: flash_attn/flash_attn_interface.py:31-33.  `gen` may be the PhiloxState of the forward (fwd_ex)."""
+    Call site: flash_attn/flash_attn_interface.py:31-33.  `gen` may be the PhiloxState of the forward (fwd_ex).
+    dq_workspace (with dq=None): a caller-owned, once-zeroed uint8 tensor of bwd_workspace_bytes(...) bytes in which dQ keeps
+    accumulating in fp32 over several calls with the same q layout (FA_FLAG_KEEP_DQ_ACCUM); bwd_dq_finalize() converts it."""
     return _bwd_impl(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seqlens_k, max_seqlen_q,
                      max_seqlen_k, p_dropout, softmax_scale, zero_tensors, is_causal, gen, seqused_q=seqused_q,
-                     seqused_k=seqused_k, alibi_slopes=alibi_slopes)
+                     seqused_k=seqused_k, alibi_slopes=alibi_slopes, dq_workspace=dq_workspace)
+
+
+def _dq_layout_params(q_like, cu_seqlens_q, max_seqlen_q, b):
+    P = FaParams()
+    total_q, h, d = q_like.shape
+    P.b, P.h, P.d, P.total_q, P.max_seqlen_q = b, h, d, total_q, int(max_seqlen_q)
+    P.cu_seqlens_q = P.cu_seqlens_k = cu_seqlens_q.data_ptr()
+    P.is_bf16 = 1 if q_like.dtype == torch.bfloat16 else 0
+    return P
+
+
+def bwd_workspace_bytes(q_like, cu_seqlens_q, max_seqlen_q):
+    """bytes of scratch a backward over this query layout needs (q_like: any (total_q, h, d) tensor)"""
+    return int(_lib.fa_workspace_bytes(ctypes.byref(_dq_layout_params(q_like, cu_seqlens_q, max_seqlen_q, cu_seqlens_q.numel() - 1)), FA_OP_BWD))
+
+
+def bwd_dq_finalize(dq, cu_seqlens_q, max_seqlen_q, softmax_scale, dq_workspace):
+    """dq (total_q, h, d) = softmax_scale * the fp32 sums that bwd(..., dq_workspace=) calls left in dq_workspace; the
+    accumulator is zero afterwards (fa_bwd_dq_finalize)."""
+    _check(dq.is_cuda and dq.dim() == 3 and dq.stride(2) == 1 and dq.dtype in (torch.float16, torch.bfloat16), "bad dq")
+    P = _dq_layout_params(dq, cu_seqlens_q, max_seqlen_q, cu_seqlens_q.numel() - 1)
+    P.dq, (P.dq_row_stride, P.dq_head_stride, _) = dq.data_ptr(), dq.stride()
+    P.softmax_scale = float(softmax_scale)
+    P.workspace, P.workspace_bytes = dq_workspace.data_ptr(), dq_workspace.numel()
+    with _DeviceGuard(dq.device) as guard:
+        _raise_if_failed(_lib.fa_bwd_dq_finalize(ctypes.byref(P), guard.raw_stream()), "fa_bwd_dq_finalize")
+    return dq
 
 
 def _check_qkv_packed(qkv, blockmask):

@@ -115,7 +115,13 @@ enum {
    * (e.g. a buffer kept between calls on the same stream).  Every backward leaves that range zero again when it
    * completes, so a persistent workspace needs to be cleared exactly once; without the flag the library clears it
    * itself (one cudaMemsetAsync per call). */
-  FA_FLAG_WS_ZEROED = 1u
+  FA_FLAG_WS_ZEROED = 1u,
+  /* backward: do not run the final pass that converts the fp32 dQ accumulator -- dQ stays in the workspace as unscaled
+   * partial sums, p->dq is not written (may be NULL) and the workspace's zero range is NOT zero on return.  Further
+   * fa_bwd calls on the SAME workspace with the same total_q / b / h / d keep adding to it (the K/V ring: one call per
+   * ring step, each with other keys); fa_bwd_dq_finalize() then produces dq and leaves the accumulator zero again.
+   * The caller owns that workspace for the whole sequence of calls. */
+  FA_FLAG_KEEP_DQ_ACCUM = 2u
 };
 
 int fa_abi_version(void);
@@ -145,6 +151,10 @@ uint64_t fa_philox_increment(const fa_params* p);
 int fa_fwd(const fa_params* p, void* stream);
 int fa_bwd(const fa_params* p, void* stream);
 int fa_fwd_block(const fa_params* p, void* stream);
+/* completes a sequence of FA_FLAG_KEEP_DQ_ACCUM backward calls: dq = softmax_scale * accumulator, 16 bit, for the query
+ * layout of p (cu_seqlens_q / seqused_q / max_seqlen_q / total_q / b / h / d, p->dq and its strides, p->workspace); the
+ * accumulator is zero afterwards.  Other fields of p are not used. */
+int fa_bwd_dq_finalize(const fa_params* p, void* stream);
 int fa_bwd_block(const fa_params* p, void* stream);
 
 /* fa_bwd for callers that cannot allocate device memory (code under CUDA-graph capture, tight serving loops, harnesses

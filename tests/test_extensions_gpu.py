@@ -398,3 +398,48 @@ def test_index_first_axis_residual_backward_kernel(dtype):
     got, _ = IndexFirstAxisResidual.backward(_Ctx, gy, gres)
     want = gres.reshape(n, -1).index_add(0, idx, gy.reshape(idx.numel(), -1)).reshape(x.shape)
     assert torch.equal(got, want)
+
+
+@pytest.mark.parametrize("d,dtype", [(128, torch.bfloat16), (64, torch.float16)])
+def test_dq_accumulates_across_backward_calls_in_the_workspace(d, dtype):
+    """FA_FLAG_KEEP_DQ_ACCUM + fa_bwd_dq_finalize (what the K/V ring does per step): the keys are split in two halves, each
+    differentiated by its own backward call with the FINAL lse, dQ kept in the caller's fp32 workspace; one finalise.  Must
+    equal the ordinary backward over all keys: dK / dV bitwise (same per-key-block work), dQ within its usual tolerance.
+    Query sub-ranges (second call: only the later half of the queries, through cu_seqlens_q + offset) hit the same slots."""
+    import flash_attn_cuda as fc
+    b, c, h = 3, 256, 2
+    torch.manual_seed(4)
+    q, k, v, dout = [torch.randn(b * 2 * c, h, d, device=DEV, dtype=dtype) for _ in range(4)]
+    cu = torch.arange(0, (b + 1) * 2 * c, 2 * c, device=DEV, dtype=torch.int32)
+    half = torch.full((b,), c, device=DEV, dtype=torch.int32)
+    scale = d ** -0.5
+    # reference: rows [0, c) of every sequence see keys [0, c); rows [c, 2c) see all keys = two "ring steps":
+    #   step A: all queries x first key half;   step B: later query half x second key half
+    (o_a, lse_a), _ = fc.fwd_ex(q, k, v, cu, cu, 2 * c, c, 0.0, scale, False, seqused_k=half)
+    (o_b, lse_b), _ = fc.fwd_ex(q, k, v, cu + c, cu + c, c, c, 0.0, scale, False, seqused_q=half, seqused_k=half)
+    o_acc = torch.empty(b * 2 * c, h, d, device=DEV)
+    lse = torch.empty(b, h, 2 * c, device=DEV)
+    fc.merge_partials(o_acc, lse, o_a, lse_a, b, 2 * c, True)
+    fc.merge_partials(o_acc[c:], lse[:, :, c:], o_b[c:], lse_b, b, c, False, batch_rows=2 * c)
+    out = o_acc.to(dtype)
+    # (1) the two-call backward with dQ kept in the workspace
+    ws = torch.zeros(fc.bwd_workspace_bytes(q, cu, 2 * c), dtype=torch.uint8, device=DEV)
+    dk1, dv1, dk2, dv2 = [torch.zeros_like(k) for _ in range(4)]
+    fc.bwd(dout, q, k, v, out, lse, None, dk1, dv1, cu, cu, 2 * c, c, 0.0, scale, False, False, None, seqused_k=half, dq_workspace=ws)
+    fc.bwd(dout, q, k, v, out, lse[:, :, c:].contiguous(), None, dk2, dv2, cu + c, cu + c, c, c, 0.0, scale, False, False, None,
+           seqused_q=half, seqused_k=half, dq_workspace=ws)
+    dq = fc.bwd_dq_finalize(torch.full_like(q, float("nan")), cu, 2 * c, scale, ws)
+    torch.cuda.synchronize()
+    assert int(ws[: fc._lib.fa_workspace_zero_range(__import__("ctypes").byref(fc._dq_layout_params(q, cu, 2 * c, b)), fc.FA_OP_BWD, None)].count_nonzero()) == 0
+    # (2) the same gradient from separate ordinary calls, dq blocks added in fp32
+    dq_a, dq_b = torch.zeros_like(q), torch.zeros_like(q)
+    dk1r, dv1r, dk2r, dv2r = [torch.zeros_like(k) for _ in range(4)]
+    fc.bwd(dout, q, k, v, out, lse, dq_a, dk1r, dv1r, cu, cu, 2 * c, c, 0.0, scale, False, False, None, seqused_k=half)
+    fc.bwd(dout, q, k, v, out, lse[:, :, c:].contiguous(), dq_b, dk2r, dv2r, cu + c, cu + c, c, c, 0.0, scale, False, False, None,
+           seqused_q=half, seqused_k=half)
+    want = dq_a.float()
+    want.view(b, 2 * c, h, d)[:, c:] += dq_b.view(b, 2 * c, h, d)[:, c:].float()
+    assert torch.isfinite(dq.float()).all()
+    assert torch.allclose(dq.float(), want, rtol=2e-2, atol=2e-3 * max(1.0, want.abs().max().item()))
+    for a, r in ((dk1, dk1r), (dv1, dv1r), (dk2, dk2r), (dv2, dv2r)):
+        assert torch.equal(a, r)

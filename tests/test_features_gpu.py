@@ -452,3 +452,38 @@ def test_bert_padding_kernels_match_torch(width, dtype):
     assert torch.equal(x.grad, mask[..., None].expand_as(x).to(dtype))
     x3 = torch.randn(b * s, 3, 4, 8, device=DEV, dtype=dtype)
     assert torch.equal(index_first_axis(x3, idx), x3[idx])
+
+
+def test_blocksparse_actually_skips_masked_blocks():
+    """Not just the right result: the butterfly layout must cost a fraction of the all-ones layout through the very same
+    entry point (forward + backward), i.e. masked (16 x 256) blocks are skipped, not computed and thrown away."""
+    from flash_attn.flash_blocksparse_attention import ButterflySparsityConfig
+    from flash_attn.flash_blocksparse_attn_interface import convert_blockmask, flash_blocksparse_attn_func
+    b, s, h, d = 4, 8192, 8, 64
+    torch.manual_seed(0)
+    qkv = torch.randn(b * s, 3, h, d, device=DEV, dtype=torch.float16, requires_grad=True)
+    dout = torch.randn(b * s, h, d, device=DEV, dtype=torch.float16)
+    cu = torch.arange(0, (b + 1) * s, s, device=DEV, dtype=torch.int32)
+    layout = ButterflySparsityConfig().make_layout(s).to(DEV)
+    density = float(layout.float().mean())
+    masks = {"butterfly": convert_blockmask(layout, causal=False), "dense": convert_blockmask(torch.ones_like(layout), causal=False)}
+
+    def step(mask):
+        out = flash_blocksparse_attn_func(qkv, cu, mask, 0.0, s, convert_mask=False)
+        torch.autograd.grad(out, qkv, dout)
+
+    ms = {}
+    for name, mask in masks.items():
+        for _ in range(2):
+            step(mask)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(5):
+            step(mask)
+        e1.record()
+        torch.cuda.synchronize()
+        ms[name] = e0.elapsed_time(e1) / 5
+    ratio = ms["butterfly"] / ms["dense"]
+    assert density < 0.5, density
+    assert ratio < min(0.8, density + 0.35), f"butterfly (density {density:.2f}) takes {ratio:.2f} of the dense time: nothing is skipped"

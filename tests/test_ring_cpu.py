@@ -54,7 +54,10 @@ class TorchBlockOps:
         o = torch.einsum('bhts,bshd->bthd', torch.exp(s - lse[..., None]), vv)
         return self._place(o, b, c, plan[0], q.dtype), lse
 
-    def bwd(self, dout, q, k, v, out, lse, b, c, plan, scale):
+    def dq_begin(self, q, b, c):
+        return torch.zeros(q.shape, dtype=torch.float32)
+
+    def bwd(self, dout, q, k, v, out, lse, b, c, plan, scale, dq_state):
         q_off, q_len, k_len, causal = plan
         qq, gg, oo, kk, vv = self._parts(b, c, plan, q, (q, True), (dout, True), (out, True), (k, False), (v, False))
         lse_v = lse[:, :, q_off * c:(q_off + q_len) * c]
@@ -65,11 +68,15 @@ class TorchBlockOps:
         dq = torch.einsum('bhts,bshd->bthd', ds, kk) * scale
         dk = torch.einsum('bhts,bthd->bshd', ds, qq) * scale
         dv = torch.einsum('bhts,bthd->bshd', p, gg)
+        h, d = q.shape[1:]
+        dq_state.reshape(b, 2 * c, h, d)[:, q_off * c:(q_off + q_len) * c] += dq
         junk = float('nan')                                                      # rows the kernels leave unwritten
-        dkf, dvf = [torch.full((b, 2 * c) + t.shape[2:], junk) for t in (dk, dv)]
-        dkf[:, :k_len * c], dvf[:, :k_len * c] = dk, dv
-        return (self._place(dq, b, c, q_off, q.dtype), dkf.reshape(b * 2 * c, *dk.shape[2:]).to(q.dtype),
-                dvf.reshape(b * 2 * c, *dv.shape[2:]).to(q.dtype))
+        dkv = torch.full((2, b, 2 * c, h, d), junk)
+        dkv[0, :, :k_len * c], dkv[1, :, :k_len * c] = dk, dv
+        return dkv.reshape(2, b * 2 * c, h, d).to(q.dtype)
+
+    def dq_end(self, dq_state, q, b, c, scale):
+        return dq_state.to(q.dtype)
 
     def merge(self, o_acc, lse_acc, o_blk, lse_blk, b, c, plan, first):
         q_off, q_len = plan[0], plan[1]
@@ -87,11 +94,10 @@ class TorchBlockOps:
         oa.copy_(oa * wa + ob * wb)
         la.copy_(new)
 
-    def accumulate(self, dst, src, b, c, off, length):
-        h, d = dst.shape[1:]
-        pad = b * 2 * c - src.shape[0]
-        s4 = torch.cat([src.new_zeros(pad, h, d), src]).reshape(b, 2 * c, h, d).float()
-        dst.reshape(b, 2 * c, h, d)[:, off * c:(off + length) * c] += s4[:, off * c:(off + length) * c]
+    def accumulate_dkv(self, acc, dkv_blk, b, c, k_len):
+        h, d = acc.shape[2:]
+        a5, s5 = acc.reshape(2, b, 2 * c, h, d), dkv_blk.reshape(2, b, 2 * c, h, d).float()
+        a5[:, :, :k_len * c] += s5[:, :, :k_len * c]
 
 
 def _free_port():
