@@ -109,15 +109,6 @@ FA_DEVICE void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, ui
       ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(gsrc)), "r"(bytes), "r"(smem_u32(bar))
       : "memory");
 }
-// 1-D bulk copy shared -> global, tracked by the thread's bulk async-group (size multiple of 16, 16-byte aligned both sides)
-FA_DEVICE void bulk_store_1d(void* gdst, const void* smem_src, uint32_t bytes) {
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n"
-               ::"l"(reinterpret_cast<uint64_t>(gdst)), "r"(smem_u32(smem_src)), "r"(bytes)
-               : "memory");
-}
-// cross-proxy fence, all state spaces: orders this thread's generic-proxy view (e.g. after an acquire) before async-proxy
-// (bulk copy) accesses it issues next
-FA_DEVICE void fence_proxy_async_all() { asm volatile("fence.proxy.async;\n" ::: "memory"); }
 // 1-D bulk reduction shared -> global: gdst[i] += ssrc[i] (fp32), tracked by the thread's bulk async-group
 FA_DEVICE void bulk_reduce_add_f32(void* gdst, const void* smem_src, uint32_t bytes) {
   asm volatile(
