@@ -558,6 +558,19 @@ def run_ours(args, w):
         dist.destroy_process_group()
 
 
+def _clock_snapshot():
+    """one nvidia-smi sample (SM clock, max, active throttle reasons): recorded with every sweep point, because the same
+    binary differs by several percent between boxes of the pool and with the power state"""
+    try:
+        out = subprocess.run(["nvidia-smi", "-i", "0", f"--query-gpu={ClockSampler.FIELDS}", "--format=csv,noheader,nounits"],
+                             capture_output=True, text=True, timeout=10).stdout.strip().split(",")
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        return {"sm_mhz": float(out[0]), "sm_max_mhz": float(out[1]),
+                "reasons": [n for n, v in zip(names, out[2:6]) if v.strip().lower().startswith("active")]}
+    except Exception:      # noqa: BLE001
+        return None
+
+
 def run_sweep(args):
     """fwd / bwd / fwd+bwd TFLOP/s vs seqlen for both BASELINE shapes (one line per point, to stdout)."""
     from flash_attn.flash_attn_interface import flash_attn_unpadded_qkvpacked_func
@@ -596,15 +609,15 @@ def run_sweep(args):
                 for _ in range(3):
                     fwd_bwd()
                 est = timed(fwd_bwd, 2)
-                reps = int(min(200, max(5, 40.0 / max(est, 1e-3))))
+                reps = int(min(400, max(10, 150.0 / max(est, 1e-3))))     # ~150 ms of device time per measurement
                 tf = timed(fwd_only, reps)
                 tfb = tf if args.fwd_only else timed(fwd_bwd, reps)
                 tb = max(tfb - tf, 1e-9)
-                row = {"sweep": tag, "seqlen": s, "causal": causal, "dropout": w["p"], "reps": reps,
+                row = {"sweep": tag, "seqlen": s, "causal": causal, "dropout": w["p"], "reps": reps, "clocks": _clock_snapshot(),
                        "fwd_ms": tf, "bwd_ms": tb, "fwd_tflops": f / tf / 1e9, "bwd_tflops": 2.5 * f / tb / 1e9,
                        "fwd_bwd_tflops": 3.5 * f / tfb / 1e9, "frac_burst_peak": 3.5 * f / tfb / 1e9 / peaks["burst"]}
-                if w["p"] == 0.0 and not args.fwd_only:
-                    # the same step replayed from a CUDA graph (dropout cannot be captured: host-side Philox offset)
+                if not args.fwd_only:
+                    # the same step replayed from a CUDA graph (dropout included: device-side Philox counter)
                     side = torch.cuda.Stream()
                     side.wait_stream(torch.cuda.current_stream())
                     with torch.cuda.stream(side):
@@ -638,7 +651,7 @@ def _sweep_time(fwd, leaves, dout, graph_ok):
 
     for _ in range(3):
         fwd_bwd()
-    reps = int(min(200, max(5, 40.0 / max(timed(fwd_bwd, 2), 1e-3))))
+    reps = int(min(400, max(10, 150.0 / max(timed(fwd_bwd, 2), 1e-3))))
     tf, tfb, tg = timed(fwd, reps), timed(fwd_bwd, reps), None
     if graph_ok:
         side = torch.cuda.Stream()
@@ -674,7 +687,7 @@ def run_sweep_extra(args):
 
     def emit(row, f, reps, tf, tfb, tg):
         tb = max(tfb - tf, 1e-9)
-        row.update({"reps": reps, "fwd_ms": tf, "bwd_ms": tb, "fwd_tflops": f / tf / 1e9, "bwd_tflops": 2.5 * f / tb / 1e9,
+        row.update({"reps": reps, "clocks": _clock_snapshot(), "fwd_ms": tf, "bwd_ms": tb, "fwd_tflops": f / tf / 1e9, "bwd_tflops": 2.5 * f / tb / 1e9,
                     "fwd_bwd_tflops": 3.5 * f / tfb / 1e9, "frac_burst_peak": 3.5 * f / tfb / 1e9 / peaks["burst"]})
         if tg is not None:
             row.update({"graph_fwd_bwd_ms": tg, "graph_fwd_bwd_tflops": 3.5 * f / tg / 1e9})
