@@ -37,8 +37,14 @@ namespace {
 constexpr int kBM = 128;            // queries per tile
 constexpr int kBN = 128;            // keys per CTA
 constexpr int kBwdThreads = 512;
-constexpr int kComputeRegs = 160;
-constexpr int kDrainRegs = 136;
+#ifndef FA_BWD_COMPUTE_REGS      // register split experiments (tools/build_variants.sh); 8*32*compute + 4*32*drain + 4*32*56 <= 65536
+#define FA_BWD_COMPUTE_REGS 160
+#define FA_BWD_DRAIN_REGS 136
+#define FA_BWD_DRAIN_RING 8
+#endif
+constexpr int kComputeRegs = FA_BWD_COMPUTE_REGS;
+constexpr int kDrainRegs = FA_BWD_DRAIN_REGS;
+static_assert(8 * 32 * kComputeRegs + 4 * 32 * kDrainRegs + 4 * 32 * 56 <= 65536, "register file");
 constexpr int kOtherRegs = 56;
 constexpr int kMaxSparseTiles = 512;
 
@@ -553,7 +559,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     uint8_t* stage_gen = sDq + wq * (L::kDqBufs * 2048);
     const uint32_t stage = smem_u32(stage_gen);
     constexpr int kChunks = DPAD / 16;
-    constexpr int kRing = kChunks < 8 ? kChunks : 8;
+    constexpr int kRing = kChunks < FA_BWD_DRAIN_RING ? kChunks : FA_BWD_DRAIN_RING;
     uint32_t n_issued = 0;
     for (int it = 0; it < n_iter; ++it) {
       const int m = tile_of(it);

@@ -24,6 +24,7 @@ class FlashAttention(nn.Module):
         super().__init__()
         self.softmax_scale = softmax_scale
         self.dropout_p = attention_dropout
+        self._cu_cache = (None, None)     # ((batch, seqlen, device), cu_seqlens of a dense batch)
 
     def forward(self, qkv, key_padding_mask=None, causal=False, cu_seqlens=None, max_s=None, need_weights=False):
         """qkv: (B, S, 3, H, D) when cu_seqlens is None, else already unpadded (nnz, 3, H, D);
@@ -40,7 +41,10 @@ class FlashAttention(nn.Module):
         batch, seqlen = qkv.shape[0], qkv.shape[1]
         if key_padding_mask is None:
             flat = qkv.reshape(batch * seqlen, *qkv.shape[2:])
-            cu = torch.arange(0, (batch + 1) * seqlen, step=seqlen, dtype=torch.int32, device=qkv.device)
+            key = (batch, seqlen, qkv.device)
+            if self._cu_cache[0] != key:      # one arange launch per shape, not per call
+                self._cu_cache = (key, torch.arange(0, (batch + 1) * seqlen, step=seqlen, dtype=torch.int32, device=qkv.device))
+            cu = self._cu_cache[1]
             out = flash_attn_unpadded_qkvpacked_func(flat, cu, seqlen, p, softmax_scale=self.softmax_scale,
                                                      causal=causal)
             return out.reshape(batch, seqlen, *out.shape[1:]), None
