@@ -8,19 +8,23 @@ lifted from K blocks inside one kernel to K/V chunks living on different GPUs.
 Layout ("zig-zag", balances causal work): the sequence is cut into 2N chunks of c tokens; rank r owns chunks r and
 2N-1-r.  A local tensor is (b, 2, c, h, d): the two chunks of a batch element are adjacent, so a batch element is one
 packed "sequence" of 2c rows whose halves a kernel launch can address through `seqused_q` / `seqused_k` (fa_params).
-K/V blocks travel rank -> rank+1 with torch.distributed P2P (NCCL over NVLink on the GPU box; gloo in the CPU tests)
-while the attention kernel works on the block already here.  At step t a rank holds the block of rank src = (r - t)
-mod N and computes exactly two c x c block products' worth of work in ONE kernel launch:
+K/V blocks travel rank -> rank+1 while the attention kernel works on the block already here: on GPUs as copy-engine pulls
+out of the predecessor's CUDA-IPC-mapped buffer over NVLink, ordered by flag kernels (`PeerTransport`, the default; NCCL
+isend / irecv cost a constant ~0.6 ms per exchange on an 8 x B200 box and left the ring transfer-bound), or through
+torch.distributed P2P (`DistTransport`: NCCL, and gloo in the CPU tests).  At step t a rank holds the block of rank
+src = (r - t) mod N and computes exactly two c x c block products' worth of work in ONE kernel launch:
 
     t = 0      [qa; qb] x [ka; kb] causal     (a precedes b in the global order: plain causal attention over 2c rows)
     src < r    [qa; qb] x ka       full       (both local query chunks come after the early chunk of an earlier rank)
     src > r    qb       x [ka; kb] full       (only the late query chunk sees a later rank's chunks -- both of them)
 
 Backward: a second ring in which every K/V block is followed, one step behind, by its fp32 (dK, dV) accumulator, which
-is home again after N hops; dQ stays local.  Each block product is differentiated with the FINAL softmax_lse and
-D = rowsum(dO o O), so the per-block gradients simply add up.  The accumulator exchange of step t overlaps the
-attention kernel of step t+1 (it is only needed when that kernel's dK / dV are added), the K/V exchange overlaps the
-kernel of the same step.
+is home again after N hops.  dQ stays local and never leaves the backward kernel's own fp32 workspace accumulator between
+steps (FA_FLAG_KEEP_DQ_ACCUM): every step adds its partial sums to the same tile slots and one conversion pass runs at the
+end (fa_bwd_dq_finalize).  Each block product is differentiated with the FINAL softmax_lse and D = rowsum(dO o O), so the
+per-block gradients simply add up.  The accumulator exchange of step t overlaps the attention kernel of step t+1 (it is only
+needed when that kernel's dK / dV are added), the K/V exchange overlaps the kernel of the same step.  Not capturable in a CUDA
+graph with the peer transport (the flag values of a pass are host-side counters baked into the launches).
 
 The per-block attention, merge and accumulate operators are injectable (`ops`) so that the host logic can be tested
 on CPU (tests/test_ring_cpu.py uses an fp32 PyTorch restatement there); the default `CudaBlockOps` calls the tcgen05
