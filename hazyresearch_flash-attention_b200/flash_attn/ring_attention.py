@@ -125,6 +125,10 @@ class CudaBlockOps:
         self.lib.merge_partials(o_acc[q_off * c:], lse_acc[:, :, q_off * c:], o_blk, lse_blk, b, q_len * c, first,
                                 batch_rows=2 * c)
 
+    def dkv_end(self, dkv, dtype):
+        """the own block's fp32 (dK, dV) sums, home after the last hop -> 16 bit"""
+        return dkv[0].to(dtype), dkv[1].to(dtype)
+
     def accumulate_dkv(self, acc, dkv_blk, b, c, k_len):
         """acc fp32 (2, b*2c, h, d) += dkv_blk (same shape, 16 bit) on the first k_len*c rows of every batch element of both
         halves: one launch ((dK, dV) x batch = 2b runs of k_len*c rows)"""
@@ -264,12 +268,87 @@ _KV_READY, _KV_CONSUMED, _DKV_READY, _DKV_CONSUMED = 0, 1, 2, 3     # flag words
 _FLAG_BYTES = 256
 
 
+class _CudaRt:
+    """Everything the peer transport asks of the device: streams, events, the flag / copy primitives of libfa_b200.so and
+    the mapping of the neighbours' memory.  The protocol classes below talk to the device only through an object like this
+    one, so that tests/test_ring_protocol_cpu.py can run the very same protocol code on a simulator that executes the queued
+    stream operations of N ranks in random interleavings."""
+
+    def __init__(self, ring, device):
+        import flash_attn_cuda
+        self.lib, self.ring, self.device = flash_attn_cuda, ring, device
+
+    # --- memory -------------------------------------------------------------------------------------------
+    def alloc(self, nbytes, zero_head):
+        mem = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+        mem[:zero_head].zero_()
+        return mem
+
+    def view(self, mem, off, shape, dtype):
+        n = 1
+        for x in shape:
+            n *= x
+        return mem[off:off + n * torch.empty((), dtype=dtype).element_size()].view(dtype).view(shape)
+
+    def addr(self, t):
+        return t.data_ptr()
+
+    def neighbours(self, mem):
+        """-> (address of the predecessor's `mem`, address of the successor's): CUDA IPC handles exchanged over the group"""
+        ring = self.ring
+        handles = [None] * ring.world
+        dist.all_gather_object(handles, self.lib.ipc_export(mem), group=ring.group)
+        grank = {(dist.get_global_rank(ring.group, i) if ring.group is not None else i): i for i in range(ring.world)}
+        opened = {}                       # a handle may be mapped once per process: at world 2 both neighbours are the same rank
+        for peer in (ring.prev, ring.next):
+            if peer not in opened:
+                handle, offset = handles[grank[peer]]
+                opened[peer] = self.lib.ipc_open(self.device, handle) + offset
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=ring.group)                      # every flag word is zero before anybody writes one
+        return opened[ring.prev], opened[ring.next]
+
+    def copy_(self, dst, src):            # on the current stream
+        dst.copy_(src)
+
+    def zero_(self, t):
+        t.zero_()
+
+    # --- streams and events ---------------------------------------------------------------------------------
+    def new_stream(self):
+        return torch.cuda.Stream(self.device)
+
+    def current_stream(self):
+        return torch.cuda.current_stream(self.device)
+
+    def wait_stream(self, waiter, awaited):
+        waiter.wait_stream(awaited)
+
+    def record(self, stream):
+        ev = torch.cuda.Event()
+        ev.record(stream)
+        return ev
+
+    def wait_event(self, stream, ev):
+        stream.wait_event(ev)
+
+    # --- the primitives of include/fa_b200.h ----------------------------------------------------------------
+    def flag_write(self, addr, value, stream):
+        self.lib.flag_write(addr, value, stream.cuda_stream)
+
+    def flag_wait_geq(self, addr, value, stream):
+        self.lib.flag_wait_geq(addr, value, stream.cuda_stream)
+
+    def peer_copy(self, dst_addr, src_addr, nbytes, stream):
+        self.lib.peer_copy(dst_addr, src_addr, nbytes, stream.cuda_stream)
+
+
 class _PeerLink:
     """Memory this rank shares with its ring neighbours through CUDA IPC, for one message shape:
     [4 flag words | K/V buffer 0 | K/V buffer 1 | dK/dV buffer 0 | dK/dV buffer 1], the same layout on every rank.
     Blocks are PULLED: a rank copies the block its predecessor holds out of the predecessor's buffer with a copy-engine
     transfer over NVLink (measured 631 GB/s for 96 MiB on an 8 x B200 NVSwitch box; NCCL isend / irecv took a constant
-    ~0.6 ms per exchange, 83 - 163 GB/s, profiles/r02_ring_probe_n8.log).  Ordering across processes: monotone 64-bit
+    ~0.6 ms per exchange, 83 - 163 GB/s, profiles/r02_ring_probe_n8_nccl.log).  Ordering across processes: monotone 64-bit
     counters, never reset, written into the WAITER's memory (fa_flag_write) and waited for by a one-thread kernel on the
     waiter's copy stream (fa_flag_wait_geq; traps after 20 s instead of hanging):
         KV_READY      written by the predecessor: number of K/V blocks it has made available (cumulative over all calls)
@@ -277,37 +356,22 @@ class _PeerLink:
         DKV_READY / DKV_CONSUMED   the same for the fp32 dK/dV accumulator that follows its block.
     Calls are collective and identical on all ranks, so every rank derives the same counter values on the host."""
 
-    def __init__(self, ring, device, kv_bytes, dkv_bytes):
-        import flash_attn_cuda
-        assert ring.world > 1, "a ring of one has no peers (a process cannot map its own IPC handle)"
-        self.lib, self.ring, self.device = flash_attn_cuda, ring, device
+    def __init__(self, rt, world, kv_bytes, dkv_bytes):
+        assert world > 1, "a ring of one has no peers (a process cannot map its own IPC handle)"
+        self.rt, self.world = rt, world
         self.kv_bytes, self.dkv_bytes = kv_bytes, dkv_bytes
         self.kv_off = [_FLAG_BYTES, _FLAG_BYTES + kv_bytes]
         self.dkv_off = [_FLAG_BYTES + 2 * kv_bytes, _FLAG_BYTES + 2 * kv_bytes + dkv_bytes]
-        self.mem = torch.empty(_FLAG_BYTES + 2 * kv_bytes + 2 * dkv_bytes, dtype=torch.uint8, device=device)
-        self.mem[:_FLAG_BYTES].zero_()
-        handles = [None] * ring.world
-        dist.all_gather_object(handles, flash_attn_cuda.ipc_export(self.mem), group=ring.group)
-        grank = {(dist.get_global_rank(ring.group, i) if ring.group is not None else i): i for i in range(ring.world)}
-        opened = {}                       # a handle may be mapped once per process: at world 2 both neighbours are the same rank
-        for peer in (ring.prev, ring.next):
-            if peer not in opened:
-                handle, offset = handles[grank[peer]]
-                opened[peer] = flash_attn_cuda.ipc_open(device, handle) + offset
-        self.prev_ptr, self.next_ptr = opened[ring.prev], opened[ring.next]      # addresses of the neighbours' `mem`
-        torch.cuda.synchronize(device)
-        dist.barrier(group=ring.group)                      # every flag word is zero before anybody writes one
-        self.s_kv, self.s_dkv = torch.cuda.Stream(device), torch.cuda.Stream(device)
+        self.mem = rt.alloc(_FLAG_BYTES + 2 * kv_bytes + 2 * dkv_bytes, _FLAG_BYTES)
+        self.prev_ptr, self.next_ptr = rt.neighbours(self.mem)        # addresses of the neighbours' `mem`
+        self.s_kv, self.s_dkv = rt.new_stream(), rt.new_stream()
         self.kv_ready = self.kv_consumed = self.dkv_ready = self.dkv_consumed = 0     # cumulative, same on all ranks
 
     def my_flag(self, word):
-        return self.mem.data_ptr() + 64 * word
+        return self.rt.addr(self.mem) + 64 * word
 
     def view(self, off, shape, dtype):
-        n = 1
-        for x in shape:
-            n *= x
-        return self.mem[off:off + n * torch.empty((), dtype=dtype).element_size()].view(dtype).view(shape)
+        return self.rt.view(self.mem, off, shape, dtype)
 
 
 _links = {}
@@ -315,76 +379,74 @@ _links = {}
 
 class _PeerKV:
     def __init__(self, link, k_rows, v_rows):
-        L = self.link = link
+        L, rt = link, link.rt
+        self.link = L
         shape = (2,) + tuple(k_rows.shape)
         self.buf = [L.view(L.kv_off[i], shape, k_rows.dtype) for i in (0, 1)]
         self.idx, self.arrived = 0, None
         self.R, self.C = L.kv_ready, L.kv_consumed
-        L.kv_ready += L.ring.world - 1           # a call announces world-1 blocks and pulls world-1 blocks
-        L.kv_consumed += L.ring.world - 1
+        L.kv_ready += L.world - 1                # a call announces world-1 blocks and pulls world-1 blocks
+        L.kv_consumed += L.world - 1
         # buffer 0 may still be the source of the successor's last pull of the previous call
-        with torch.cuda.stream(L.s_kv):
-            L.lib.flag_wait_geq(L.my_flag(_KV_CONSUMED), self.C, L.s_kv.cuda_stream)
-        torch.cuda.current_stream(L.device).wait_stream(L.s_kv)
-        self.buf[0][0].copy_(k_rows)
-        self.buf[0][1].copy_(v_rows)
+        rt.flag_wait_geq(L.my_flag(_KV_CONSUMED), self.C, L.s_kv)
+        rt.wait_stream(rt.current_stream(), L.s_kv)
+        rt.copy_(self.buf[0][0], k_rows)
+        rt.copy_(self.buf[0][1], v_rows)
 
     k = property(lambda self: self.buf[self.idx][0])
     v = property(lambda self: self.buf[self.idx][1])
 
     def prefetch(self, t):
         """pull the block the predecessor holds at step t into the other buffer (it is this rank's block of step t+1)"""
-        L, lib = self.link, self.link.lib
-        rs = L.s_kv.cuda_stream
+        L, rt, s = self.link, self.link.rt, self.link.s_kv
         # the target buffer was read by the kernels of step t-1; at t = 0 the fill of buffer 0 must have finished
-        L.s_kv.wait_stream(torch.cuda.current_stream(L.device))
+        rt.wait_stream(s, rt.current_stream())
         if t == 0:
-            lib.flag_write(L.next_ptr + 64 * _KV_READY, self.R + 1, rs)           # my own K/V is block #0
-        lib.flag_wait_geq(L.my_flag(_KV_READY), self.R + t + 1, rs)              # the predecessor's block #t is there
-        lib.flag_wait_geq(L.my_flag(_KV_CONSUMED), self.C + t, rs)               # the successor is done with my target buffer
-        lib.peer_copy(self.buf[(t + 1) % 2].data_ptr(), L.prev_ptr + L.kv_off[t % 2], L.kv_bytes, rs)
-        if t + 1 <= L.ring.world - 2:
-            lib.flag_write(L.next_ptr + 64 * _KV_READY, self.R + t + 2, rs)       # block #(t+1) can be pulled from me
-        lib.flag_write(L.prev_ptr + 64 * _KV_CONSUMED, self.C + t + 1, rs)
-        self.arrived = torch.cuda.Event()
-        self.arrived.record(L.s_kv)
+            rt.flag_write(L.next_ptr + 64 * _KV_READY, self.R + 1, s)              # my own K/V is block #0
+        rt.flag_wait_geq(L.my_flag(_KV_READY), self.R + t + 1, s)                  # the predecessor's block #t is there
+        rt.flag_wait_geq(L.my_flag(_KV_CONSUMED), self.C + t, s)                   # the successor is done with my target buffer
+        rt.peer_copy(rt.addr(self.buf[(t + 1) % 2]), L.prev_ptr + L.kv_off[t % 2], L.kv_bytes, s)
+        if t + 1 <= L.world - 2:
+            rt.flag_write(L.next_ptr + 64 * _KV_READY, self.R + t + 2, s)          # block #(t+1) can be pulled from me
+        rt.flag_write(L.prev_ptr + 64 * _KV_CONSUMED, self.C + t + 1, s)
+        self.arrived = rt.record(s)
 
     def advance(self):
-        torch.cuda.current_stream(self.link.device).wait_event(self.arrived)
+        rt = self.link.rt
+        rt.wait_event(rt.current_stream(), self.arrived)
         self.idx ^= 1
 
 
 class _PeerDKV:
     def __init__(self, link, rows, h, d):
-        L = self.link = link
+        L, rt = link, link.rt
+        self.link = L
         self.buf = [L.view(L.dkv_off[i], (2, rows, h, d), torch.float32) for i in (0, 1)]
         self.idx, self.arrived = 0, None
         self.R, self.C = L.dkv_ready, L.dkv_consumed
-        L.dkv_ready += L.ring.world              # world announcements and world pulls per call (the last one goes home)
-        L.dkv_consumed += L.ring.world
-        with torch.cuda.stream(L.s_dkv):
-            L.lib.flag_wait_geq(L.my_flag(_DKV_CONSUMED), self.C, L.s_dkv.cuda_stream)
-        torch.cuda.current_stream(L.device).wait_stream(L.s_dkv)
-        self.buf[0].zero_()
+        L.dkv_ready += L.world                   # world announcements and world pulls per call (the last one goes home)
+        L.dkv_consumed += L.world
+        rt.flag_wait_geq(L.my_flag(_DKV_CONSUMED), self.C, L.s_dkv)
+        rt.wait_stream(rt.current_stream(), L.s_dkv)
+        rt.zero_(self.buf[0])
 
     cur = property(lambda self: self.buf[self.idx])
 
     def depart(self, t):
         """step t's sums are in `cur`: announce them to the successor, and pull the predecessor's (the accumulator of the
         block this rank holds at step t+1) under the next step's kernel"""
-        L, lib = self.link, self.link.lib
-        rs = L.s_dkv.cuda_stream
-        L.s_dkv.wait_stream(torch.cuda.current_stream(L.device))                     # the accumulate kernels of step t
-        lib.flag_write(L.next_ptr + 64 * _DKV_READY, self.R + t + 1, rs)
-        lib.flag_wait_geq(L.my_flag(_DKV_READY), self.R + t + 1, rs)
-        lib.flag_wait_geq(L.my_flag(_DKV_CONSUMED), self.C + t, rs)              # the successor has pulled what my target buffer held
-        lib.peer_copy(self.buf[(t + 1) % 2].data_ptr(), L.prev_ptr + L.dkv_off[t % 2], L.dkv_bytes, rs)
-        lib.flag_write(L.prev_ptr + 64 * _DKV_CONSUMED, self.C + t + 1, rs)
-        self.arrived = torch.cuda.Event()
-        self.arrived.record(L.s_dkv)
+        L, rt, s = self.link, self.link.rt, self.link.s_dkv
+        rt.wait_stream(s, rt.current_stream())                                       # the accumulate kernels of step t
+        rt.flag_write(L.next_ptr + 64 * _DKV_READY, self.R + t + 1, s)
+        rt.flag_wait_geq(L.my_flag(_DKV_READY), self.R + t + 1, s)
+        rt.flag_wait_geq(L.my_flag(_DKV_CONSUMED), self.C + t, s)                  # the successor has pulled what my target buffer held
+        rt.peer_copy(rt.addr(self.buf[(t + 1) % 2]), L.prev_ptr + L.dkv_off[t % 2], L.dkv_bytes, s)
+        rt.flag_write(L.prev_ptr + 64 * _DKV_CONSUMED, self.C + t + 1, s)
+        self.arrived = rt.record(s)
 
     def arrive(self):
-        torch.cuda.current_stream(self.link.device).wait_event(self.arrived)
+        rt = self.link.rt
+        rt.wait_event(rt.current_stream(), self.arrived)
         self.idx ^= 1
 
     def home(self):
@@ -395,12 +457,13 @@ class _PeerDKV:
 class PeerTransport:
     name = "peer"
 
-    def __init__(self, ring, device, rows, h, d, dtype):
+    def __init__(self, ring, device, rows, h, d, dtype, rt=None, links=None):
         es = torch.empty((), dtype=dtype).element_size()
-        key = (id(ring.group), ring.world, ring.rank, device.index, rows, h, d, dtype)
-        if key not in _links:
-            _links[key] = _PeerLink(ring, device, 2 * rows * h * d * es, 2 * rows * h * d * 4)
-        self.link = _links[key]
+        links = _links if links is None else links
+        key = (id(ring.group), ring.world, ring.rank, getattr(device, "index", None), rows, h, d, dtype)
+        if key not in links:
+            links[key] = _PeerLink(rt or _CudaRt(ring, device), ring.world, 2 * rows * h * d * es, 2 * rows * h * d * 4)
+        self.link = links[key]
 
     def kv_stream(self, k_rows, v_rows):
         return _PeerKV(self.link, k_rows, v_rows)
@@ -413,6 +476,8 @@ default_transport = None      # None = "peer" for CUDA tensors on an NCCL group 
 
 
 def _make_transport(ring, q, rows, transport):
+    if transport is not None and not isinstance(transport, str):
+        return transport                    # a ready-made transport object (tests/test_ring_protocol_cpu.py)
     transport = transport or default_transport
     if transport is None:
         peer_ok = q.is_cuda and ring.world > 1 and dist.is_initialized() and dist.get_backend(ring.group) == "nccl"
@@ -429,7 +494,7 @@ def _make_transport(ring, q, rows, transport):
 def ring_forward(q, k, v, softmax_scale, group=None, ops=None, transport=None):
     """q, k, v: local (b, 2, c, h, d) zig-zag shards.  -> out (b, 2, c, h, d) (dtype of q), lse (b, h, 2c) fp32."""
     ops = _ops_or_default(ops)
-    ring = _Ring(group)
+    ring = getattr(transport, "ring", None) or _Ring(group)
     b, two, c, h, d = q.shape
     assert two == 2 and k.shape == q.shape and v.shape == q.shape
     assert c % 16 == 0, "chunk length must be a multiple of 16"
@@ -455,7 +520,7 @@ def ring_forward(q, k, v, softmax_scale, group=None, ops=None, transport=None):
 def ring_backward(dout, q, k, v, out, lse, softmax_scale, group=None, ops=None, transport=None):
     """-> dq, dk, dv, each (b, 2, c, h, d) in the dtype of q.  `lse` is ring_forward's (b, h, 2c) final log-sum-exp."""
     ops = _ops_or_default(ops)
-    ring = _Ring(group)
+    ring = getattr(transport, "ring", None) or _Ring(group)
     b, two, c, h, d = q.shape
     rows = b * 2 * c
     qf, of, gf = (t.reshape(rows, h, d) for t in (q, out, dout.contiguous()))
@@ -482,8 +547,9 @@ def ring_backward(dout, q, k, v, out, lse, softmax_scale, group=None, ops=None, 
     dq = ops.dq_end(dq_state, qf, b, c, softmax_scale)
     with _span("bwd_wait_dkv", ring.world):
         dkv = acc.home()
+    dk, dv = ops.dkv_end(dkv, q.dtype)
     shape = (b, 2, c, h, d)
-    return dq.reshape(shape), dkv[0].to(q.dtype).reshape(shape), dkv[1].to(q.dtype).reshape(shape)
+    return dq.reshape(shape), dk.reshape(shape), dv.reshape(shape)
 
 
 class RingFlashAttnFunc(torch.autograd.Function):

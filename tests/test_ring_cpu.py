@@ -94,6 +94,9 @@ class TorchBlockOps:
         oa.copy_(oa * wa + ob * wb)
         la.copy_(new)
 
+    def dkv_end(self, dkv, dtype):
+        return dkv[0].to(dtype), dkv[1].to(dtype)
+
     def accumulate_dkv(self, acc, dkv_blk, b, c, k_len):
         h, d = acc.shape[2:]
         a5, s5 = acc.reshape(2, b, 2 * c, h, d), dkv_blk.reshape(2, b, 2 * c, h, d).float()
