@@ -88,7 +88,7 @@ class FlashMHA(nn.Module):
         b, s, _ = x.shape
         qkv = self.Wqkv(x)
         if self.use_rotary_emb:
-            # one in-place kernel pass over q and k (the reference: elementwise torch ops + torch.stack, :105-110)
+            # one kernel pass (the reference: elementwise torch ops + torch.stack, :105-110)
             key = (s, qkv.device)
             if self._rotary_cache[0] != key:
                 self._rotary_cache = (key, rotary_tables(self.use_rotary_emb, s, self.head_dim, qkv.device))

@@ -55,9 +55,9 @@ class FlashAttnQKVPackedFunc(torch.autograd.Function):
     @staticmethod
     def forward(ctx, qkv, cu_seqlens, max_seqlen, dropout_p, softmax_scale, causal, return_softmax, alibi_slopes=None):
         softmax_scale = _default_scale(softmax_scale, qkv.shape[-1])
-        out, lse, s_dmask, rng = _flash_attn_forward(qkv[:, 0], qkv[:, 1], qkv[:, 2], cu_seqlens, cu_seqlens,
-                                                     max_seqlen, max_seqlen, dropout_p, softmax_scale, causal,
-                                                     return_softmax, alibi_slopes)
+        q, k, v = qkv.unbind(1)      # three strided views in one call
+        out, lse, s_dmask, rng = _flash_attn_forward(q, k, v, cu_seqlens, cu_seqlens, max_seqlen, max_seqlen, dropout_p,
+                                                     softmax_scale, causal, return_softmax, alibi_slopes)
         ctx.save_for_backward(qkv, out, lse, cu_seqlens)
         _save_hparams(ctx, dropout_p, max_seqlen, max_seqlen, softmax_scale, causal, rng, alibi_slopes)
         return (out, lse, s_dmask) if return_softmax else out
@@ -66,8 +66,8 @@ class FlashAttnQKVPackedFunc(torch.autograd.Function):
     def backward(ctx, dout, *unused):
         qkv, out, lse, cu_seqlens = ctx.saved_tensors
         dqkv = torch.empty_like(qkv)
-        _flash_attn_backward(dout, qkv[:, 0], qkv[:, 1], qkv[:, 2], out, lse, dqkv[:, 0], dqkv[:, 1],
-                             dqkv[:, 2], cu_seqlens, cu_seqlens, ctx.max_seqlen_q, ctx.max_seqlen_k,
+        (q, k, v), (dq, dk, dv) = qkv.unbind(1), dqkv.unbind(1)
+        _flash_attn_backward(dout, q, k, v, out, lse, dq, dk, dv, cu_seqlens, cu_seqlens, ctx.max_seqlen_q, ctx.max_seqlen_k,
                              ctx.dropout_p, ctx.softmax_scale, ctx.causal, ctx.rng, ctx.alibi_slopes)
         return dqkv, None, None, None, None, None, None, None
 
