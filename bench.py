@@ -737,6 +737,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="d128", choices=sorted(WORKLOADS))
     ap.add_argument("--sweep", action="store_true")
+    ap.add_argument("--sweep-extra", action="store_true", help="only the varlen / cross-attention / blocksparse points of the sweep")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile", action="store_true", help="runs under ncu: the headline steps only (no e2e / ring / sub-records / CPU legs; "
                                                            "the line it prints is not a bench value)")
@@ -746,6 +747,8 @@ def main():
     w = WORKLOADS[args.workload]
     if args.impl == "reference":
         run_reference(args, w)
+    elif args.sweep_extra:
+        run_sweep_extra(args)
     elif args.sweep:
         run_sweep(args)
         run_sweep_extra(args)

@@ -105,6 +105,9 @@ __device__ long long g_bwd_cta[8192 * 12];   // per CTA: smid, globaltimer start
 #define FA_TRACE(slot) do { } while (0)
 #define FA_CTA_MARK(slot, val) do { } while (0)
 #endif
+#ifndef FA_POST_TRIM_BATCH
+#define FA_POST_TRIM_BATCH 4   // trimmed postprocess pass: 16-column chunks in flight per thread (1 / 2 / 4 measured: profiles/r02_head_dim_trim_ab.log)
+#endif
 
 __device__ __forceinline__ float4 lds128(uint32_t addr) {
   float4 v;
@@ -118,22 +121,29 @@ __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t
 // dQ finalisation of one tile quarter (32 query rows): fp32 accumulator (L2) -> x scale -> 16 bit -> dq, and zeros written
 // back so that the accumulator is clean for the next call.  Quarter layout: [DPAD/16 chunks][4 column groups][32 rows][4].
 // `dq_row`: this lane's output row, nullptr when the row lies beyond the sequence.  kBatch chunks are in flight at a time.
-template <int DPAD, bool kBf16, int kBatch>
+template <int DPAD, bool kBf16, int kBatch, bool kTrim>
 __device__ __forceinline__ void finalize_dq_quarter(float* acc, uint16_t* dq_row, int d, float scale, int lane) {
-  constexpr int kChunks = DPAD / 16;
+  // kTrim: the main kernel ran trimmed and never touched the chunks past ceil16(d) -- they are still zero.  (A template flag, not a
+  // run-time count: the predicated form needs 84 registers instead of 70, one resident CTA less per SM, +25 % on the full-width pass.)
+  constexpr int kB = kTrim ? FA_POST_TRIM_BATCH : kBatch;        // chunks in flight per thread
+  constexpr bool kGuard = kTrim && kB > 2;                       // else: the chunk count is rounded up to whole batches (zeros)
+  const int n_exact = kTrim ? (d + 15) >> 4 : DPAD / 16;
+  const int n_chunks = kGuard ? n_exact : (n_exact + kB - 1) / kB * kB;
 #pragma unroll 1
-  for (int k0 = 0; k0 < kChunks; k0 += kBatch) {
-    float4 v[kBatch][4];
+  for (int k0 = 0; k0 < n_chunks; k0 += kB) {
+    float4 v[kB][4];
 #pragma unroll
-    for (int b = 0; b < kBatch; ++b)
+    for (int b = 0; b < kB; ++b)
 #pragma unroll
-      for (int g = 0; g < 4; ++g) v[b][g] = __ldcg(reinterpret_cast<const float4*>(acc + (k0 + b) * 512 + g * 128 + lane * 4));
+      for (int g = 0; g < 4; ++g)
+        v[b][g] = (!kGuard || k0 + b < n_chunks) ? __ldcg(reinterpret_cast<const float4*>(acc + (k0 + b) * 512 + g * 128 + lane * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-    for (int b = 0; b < kBatch; ++b)
+    for (int b = 0; b < kB; ++b)
 #pragma unroll
-      for (int g = 0; g < 4; ++g) __stcg(reinterpret_cast<float4*>(acc + (k0 + b) * 512 + g * 128 + lane * 4), make_float4(0.f, 0.f, 0.f, 0.f));
+      for (int g = 0; g < 4; ++g)
+        if (!kGuard || k0 + b < n_chunks) __stcg(reinterpret_cast<float4*>(acc + (k0 + b) * 512 + g * 128 + lane * 4), make_float4(0.f, 0.f, 0.f, 0.f));
 #pragma unroll
-    for (int b = 0; b < kBatch; ++b) {
+    for (int b = 0; b < kB; ++b) {
       const int col = (k0 + b) * 16;
       uint4 lo, hi;
       lo.x = pack2<kBf16>(v[b][0].x * scale, v[b][0].y * scale);
@@ -153,7 +163,9 @@ __device__ __forceinline__ void finalize_dq_quarter(float* acc, uint16_t* dq_row
 // ------------------------------------------------------------------------------------------------
 // main kernel
 // ------------------------------------------------------------------------------------------------
-template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse, bool kAlibi>
+// kTrim: head dim below DPAD -- issue only the MMA k-steps / output columns / dQ reduction chunks that hold data (a separate
+// instantiation: with the counts as run-time values the full-width kernels lose 3 % to the extra registers and branches)
+template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse, bool kAlibi, bool kTrim>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, const BlockMaskView bm, const BwdWs ws,
                  const int n_kblocks, const int bh_group, const PhiloxKey pk) {   // round keys precomputed on the host (constant bank)
@@ -380,9 +392,12 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
       // instructions are emitted back to back from uniform registers.)
       if (n_iter > 0 && elect_one()) {
         constexpr bool leader = true;
-        const uint32_t idesc_st = make_idesc_f16(kBf16, 128, 128, false, false);    // S^T, dP^T
-        const uint32_t idesc_kv = make_idesc_f16(kBf16, 128, DPAD, false, true);    // dV, dK (B = dO / Q, MN-major)
-        const uint32_t idesc_dq = make_idesc_f16(kBf16, 128, DPAD, true, true);     // dQ (A = dS^T read MN-major)
+        // head dims below DPAD: columns [d, DPAD) of Q, K, V and dO are zeros (TMA fill), so S^T / dP^T only need the k-steps
+        // that hold data and dV / dK / dQ only their first ceil16(d) columns; what lies past them in TMEM is never stored
+        const int ksteps = kTrim ? (p.d + 15) >> 4 : DPAD / 16;
+        const uint32_t idesc_st = make_idesc_f16(kBf16, 128, 128, false, false);            // S^T, dP^T
+        const uint32_t idesc_kv = make_idesc_f16(kBf16, 128, ksteps * 16, false, true);     // dV, dK (B = dO / Q, MN-major)
+        const uint32_t idesc_dq = make_idesc_f16(kBf16, 128, ksteps * 16, true, true);      // dQ (A = dS^T read MN-major)
         const uint32_t aQ = smem_u32(sQ);
         const uint32_t tS = tmem_base + kColS, tDP = tmem_base + kColDP, tDV = tmem_base + kColDV, tDK = tmem_base + kColDK;
         // descriptor bases (low words; the high word is constant); a byte offset o inside a tile is added as (o >> 4)
@@ -402,6 +417,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
           if (leader) {
 #pragma unroll
             for (int kk = 0; kk < DPAD / 16; ++kk) {
+              if (kk >= ksteps) break;
               const uint32_t off = ((kk >> 2) * L::kSub + (kk & 3) * 32) >> 4;
               umma_ss_lo(d_tmem, a_desc + off, b_desc + off, idesc_st, kk > 0 ? 1u : 0u);
             }
@@ -560,6 +576,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
     const uint32_t stage = smem_u32(stage_gen);
     constexpr int kChunks = DPAD / 16;
     constexpr int kRing = kChunks < FA_BWD_DRAIN_RING ? kChunks : FA_BWD_DRAIN_RING;
+    const int n_chunks = kTrim ? (p.d + 15) >> 4 : kChunks;   // 16-column chunks that hold data: the others are neither staged nor reduced
     uint32_t n_issued = 0;
     for (int it = 0; it < n_iter; ++it) {
       const int m = tile_of(it);
@@ -577,6 +594,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
       }
 #pragma unroll
       for (int k = 0; k < kChunks; ++k) {
+        if (k < n_chunks) {
         const uint32_t buf = n_issued % L::kDqBufs;
         if (n_issued >= L::kDqBufs) {
           if (lane == 0) bulk_wait_group_read<L::kDqBufs - 1>();   // the bulk op that last read this buffer is done with it
@@ -598,6 +616,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
         if (v[k % kRing][0] == 0x7fc12345u) st_shared_v4(dst, 0, 0, 0, 0);   // timing experiment: no staging, no reduction
         if (lane == 0) bulk_commit_group();
 #endif
+        }
         if (k + kRing < kChunks) {
           tmem_ld16(tDQ + (k + kRing) * 16, v[k % kRing]);
           tmem_wait_ld();
@@ -904,7 +923,7 @@ __global__ void __launch_bounds__(256) bwd_preprocess_kernel(const fa_params p, 
 // ------------------------------------------------------------------------------------------------
 // postprocess: dq = scale * dq_accum -> 16 bit, caller's strides; zeros written back (accumulator clean for the next call)
 // ------------------------------------------------------------------------------------------------
-template <bool kBf16, int DPAD>
+template <bool kBf16, int DPAD, bool kTrim>
 __global__ void __launch_bounds__(128) bwd_postprocess_kernel(const fa_params p, const BwdWs ws, const int n_qtiles) {
   const int bidb = blockIdx.x / n_qtiles, bidh = blockIdx.y;
   const int m = blockIdx.x - bidb * n_qtiles;
@@ -915,7 +934,7 @@ __global__ void __launch_bounds__(128) bwd_postprocess_kernel(const fa_params p,
   float* acc = ws.dq_accum + ((int64_t)bidh * ws.n_slots + tile_slot(seq.q_begin, bidb, m)) * (kBM * DPAD) + q4 * (32 * DPAD);
   uint16_t* out = row < seq.seqlen_q ? reinterpret_cast<uint16_t*>(p.dq) + (int64_t)(seq.q_begin + row) * p.dq_row_stride + (int64_t)bidh * p.dq_head_stride
                                      : nullptr;
-  finalize_dq_quarter<DPAD, kBf16, 4>(acc, out, p.d, p.softmax_scale, lane);
+  finalize_dq_quarter<DPAD, kBf16, 4, kTrim>(acc, out, p.d, p.softmax_scale, lane);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -940,10 +959,17 @@ BwdWsLayout bwd_ws_layout(const fa_params& p) {
   return l;
 }
 
-template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse, bool kAlibi>
+// The trimmed instantiations exist where they pay: the 128-column tile without dropout and without a block mask (there the
+// kernel is bound by the dQ reduction traffic, which shrinks with the head dim; the dropout variants are ALU-bound and the
+// 64-column tile gains < 1 %).  The postprocess pass has to agree, hence one predicate for both.
+inline bool bwd_runs_trimmed(const fa_params& p, const BlockMaskView& bm) {
+  return p.d > 64 && ((p.d + 15) >> 4) < 8 && !(p.p_dropout > 0.f) && bm.dense == nullptr;
+}
+
+template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse, bool kAlibi, bool kTrim = false>
 cudaError_t launch_bwd_variant(const BwdTensorMaps& maps, const fa_params& p, const BlockMaskView& bm, const BwdWs& ws,
                                cudaStream_t stream) {
-  auto kernel = bwd_sm100_kernel<DPAD, kBf16, kCausal, kDropout, kSparse, kAlibi>;
+  auto kernel = bwd_sm100_kernel<DPAD, kBf16, kCausal, kDropout, kSparse, kAlibi, kTrim>;
   constexpr int smem = BwdSmem<DPAD>::kDynamicBytes;
   static std::atomic<uint64_t> configured{0};   // bit per device (as in the forward)
   int dev = 0;
@@ -974,6 +1000,16 @@ cudaError_t dispatch_bwd_flags(const BwdTensorMaps& maps, const fa_params& p, co
                 : launch_bwd_variant<DPAD, kBf16, false, false, true, false>(maps, p, bm, ws, stream);
   }
   const int sel = (p.is_causal ? 4 : 0) | (drop ? 2 : 0) | (p.alibi_slopes != nullptr ? 1 : 0);
+  if constexpr (DPAD == 128) {
+    if (bwd_runs_trimmed(p, bm)) {
+      switch (sel) {
+        case 0: return launch_bwd_variant<DPAD, kBf16, false, false, false, false, true>(maps, p, bm, ws, stream);
+        case 1: return launch_bwd_variant<DPAD, kBf16, false, false, false, true, true>(maps, p, bm, ws, stream);
+        case 4: return launch_bwd_variant<DPAD, kBf16, true, false, false, false, true>(maps, p, bm, ws, stream);
+        default: return launch_bwd_variant<DPAD, kBf16, true, false, false, true, true>(maps, p, bm, ws, stream);
+      }
+    }
+  }
   switch (sel) {
     case 0: return launch_bwd_variant<DPAD, kBf16, false, false, false, false>(maps, p, bm, ws, stream);
     case 1: return launch_bwd_variant<DPAD, kBf16, false, false, false, true>(maps, p, bm, ws, stream);
@@ -1064,11 +1100,14 @@ cudaError_t launch_bwd_sm100(const fa_params& p, const BlockMaskView& bm, void* 
   if (!(p.flags & FA_FLAG_KEEP_DQ_ACCUM) && n_qtiles > 0 && p.total_q > 0) {
     const dim3 grid(static_cast<unsigned>(n_qtiles * p.b), p.h, 1);
     if (l.dpad == 64) {
-      if (p.is_bf16) bwd_postprocess_kernel<true, 64><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
-      else bwd_postprocess_kernel<false, 64><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
+      if (p.is_bf16) bwd_postprocess_kernel<true, 64, false><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
+      else bwd_postprocess_kernel<false, 64, false><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
+    } else if (bwd_runs_trimmed(p, bm)) {
+      if (p.is_bf16) bwd_postprocess_kernel<true, 128, true><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
+      else bwd_postprocess_kernel<false, 128, true><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
     } else {
-      if (p.is_bf16) bwd_postprocess_kernel<true, 128><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
-      else bwd_postprocess_kernel<false, 128><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
+      if (p.is_bf16) bwd_postprocess_kernel<true, 128, false><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
+      else bwd_postprocess_kernel<false, 128, false><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
     }
     count_launch();
     e = cudaGetLastError();
@@ -1089,12 +1128,13 @@ cudaError_t launch_bwd_dq_finalize(const fa_params& p, void* workspace, cudaStre
   ws.dq_accum = reinterpret_cast<float*>(base + l.accum_off);
   ws.n_slots = l.n_slots;
   const dim3 grid(static_cast<unsigned>(n_qtiles * p.b), p.h, 1);
+  // every chunk: the launches that accumulated may or may not have run trimmed
   if (l.dpad == 64) {
-    if (p.is_bf16) bwd_postprocess_kernel<true, 64><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
-    else bwd_postprocess_kernel<false, 64><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
+    if (p.is_bf16) bwd_postprocess_kernel<true, 64, false><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
+    else bwd_postprocess_kernel<false, 64, false><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
   } else {
-    if (p.is_bf16) bwd_postprocess_kernel<true, 128><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
-    else bwd_postprocess_kernel<false, 128><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
+    if (p.is_bf16) bwd_postprocess_kernel<true, 128, false><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
+    else bwd_postprocess_kernel<false, 128, false><<<grid, 128, 0, stream>>>(p, ws, n_qtiles);
   }
   count_launch();
   return cudaGetLastError();

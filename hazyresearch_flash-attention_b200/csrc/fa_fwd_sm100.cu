@@ -281,8 +281,12 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
     } else if (warp == 9) {
       // ===================================== MMA issuer =======================================
       if (elect_one()) {
+        // head dims below DPAD: the columns [d, DPAD) of Q, K and V are zeros (TMA fills what lies beyond the tensor's extent), so
+        // S = Q K^T only needs the k-steps that hold data and O += P V only the first ceil16(d) output columns.  The O columns
+        // past that are never written by an MMA and never stored (the epilogue stores d columns).
+        const int ksteps = (p.d + 15) >> 4;
         const uint32_t idesc_qk = make_idesc_f16(kBf16, kBlockM, kBlockN, false, false);
-        const uint32_t idesc_pv = make_idesc_f16(kBf16, kBlockM, DPAD, false, true);
+        const uint32_t idesc_pv = make_idesc_f16(kBf16, kBlockM, ksteps * 16, false, true);
         const uint32_t sQ_addr = smem_u32(sQ), sK_addr = smem_u32(sK), sV_addr = smem_u32(sV);
 
         // S_t = Q_t K^T : A = Q tile (K-major), B = K tile (K-major); DPAD/16 MMAs of K=16
@@ -290,6 +294,7 @@ fwd_sm100_kernel(const __grid_constant__ FwdTensorMaps maps, const fa_params p, 
           const uint32_t a0 = sQ_addr + t * L::kTileBytes, b0 = sK_addr + stage * L::kTileBytes;
 #pragma unroll
           for (int kk = 0; kk < DPAD / 16; ++kk) {
+            if (kk >= ksteps) break;
             const uint32_t off = (kk >> 2) * L::kSubTileBytes + (kk & 3) * 32;
             umma_ss(tmem_base + t * 128, make_smem_desc_sw128(a0 + off, 16, 1024),
                     make_smem_desc_sw128(b0 + off, 16, 1024), idesc_qk, kk > 0 ? 1u : 0u);

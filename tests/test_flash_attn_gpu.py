@@ -186,3 +186,31 @@ def test_flash_attn_race_condition(seqlen, d, dropout_p, causal, dtype):
                 assert torch.allclose(a.float(), b.float(), rtol=2e-2, atol=1e-3 * max(1.0, a.abs().max().item()))
             else:
                 assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("d", [8, 16, 24, 40, 48, 72, 88, 104, 112, 120])
+def test_every_multiple_of_8_head_dim(d, causal, dtype):
+    """fmha_api.cpp:163-164 accepts every head dim that is a multiple of 8 up to 128.  The kernels run them in a 64- or
+    128-column tile and issue only the MMA k-steps / output columns / dQ reduction chunks that hold data
+    (ceil16(d)); this walks the head dims the reference grid does not (d % 16 == 8 included), p = 0.17, ragged lengths,
+    and finishes with a d = 128 call on the same stream: the dQ workspace the trimmed call left behind must be clean."""
+    fi = _api()
+    seqlen = 257
+    for dd in (d, 128):
+        q, k, v = make_inputs(seqlen, dd, dtype)
+        mask = orc.generate_random_padding_mask(seqlen, BATCH, "cuda", mode="random")
+        P = U.generate_qkv(q, k, v, mask, mask, qkvpacked=True)
+        out_unpad, lse, S_dmask = fi.flash_attn_unpadded_qkvpacked_func(P.qkv_unpad, P.cu_q, P.max_q, 0.17,
+                                                                        return_attn_probs=True, causal=causal)
+        out = P.pad_q(out_unpad)
+        dropout_mask, attn = U.decode_s_dmask(S_dmask, seqlen, seqlen)
+        g = torch.randn_like(out)
+        dqkv_unpad, = torch.autograd.grad(out_unpad, P.qkv_unpad, g[mask])
+        dq, dk, dv = [P.pad_q(dqkv_unpad[:, i]) for i in range(3)]
+        out_ref, attn_ref, gr, out_pt, attn_pt, gp = reference_triplet(q, k, v, mask, mask, 0.17, dropout_mask, causal, g)
+        check_2x(f"O d{dd}", out, out_ref, out_pt)
+        check_2x(f"attn d{dd}", attn, attn_ref, attn_pt)
+        for name, got, ref, pt in zip(("dQ", "dK", "dV"), (dq, dk, dv), gr, gp):
+            check_2x(f"{name} d{dd}", got, ref, pt)
