@@ -95,7 +95,10 @@ int validate_common(const fa_params* p, bool bwd, bool block) {
                   t.name, (long long)t.rs, (long long)t.hs);
   }
   if (bwd && p->softmax_d == nullptr) return fail(FA_ERR_INVALID_ARGUMENT, "softmax_d is NULL");
-  if (p->flags & ~(FA_FLAG_WS_ZEROED | FA_FLAG_KEEP_DQ_ACCUM)) return fail(FA_ERR_INVALID_ARGUMENT, "unknown flags 0x%x", p->flags);
+  if (p->flags & ~(FA_FLAG_WS_ZEROED | FA_FLAG_KEEP_DQ_ACCUM | FA_FLAG_DETERMINISTIC)) return fail(FA_ERR_INVALID_ARGUMENT, "unknown flags 0x%x", p->flags);
+  if ((p->flags & FA_FLAG_DETERMINISTIC) && (!bwd || block || p->impl == FA_IMPL_SIMT || (p->flags & FA_FLAG_KEEP_DQ_ACCUM)))
+    return fail(FA_ERR_INVALID_ARGUMENT, "FA_FLAG_DETERMINISTIC applies to fa_bwd with the tcgen05 kernels, without a block mask and without "
+                                         "FA_FLAG_KEEP_DQ_ACCUM");
   if ((p->flags & FA_FLAG_KEEP_DQ_ACCUM) && (!bwd || block || p->impl == FA_IMPL_SIMT))
     return fail(FA_ERR_INVALID_ARGUMENT, "FA_FLAG_KEEP_DQ_ACCUM applies to fa_bwd with the tcgen05 kernels only");
   if ((p->flags & FA_FLAG_KEEP_DQ_ACCUM) && !(p->flags & FA_FLAG_WS_ZEROED))

@@ -84,6 +84,8 @@ struct BwdWs {
   float* nl;         // (h, n_slots * 128): -lse*log2e, -inf for rows that must produce P = 0
   float* dsum;       // (h, n_slots * 128): D = rowsum(dO o O), 0 for invalid rows
   float* dq_accum;   // (h, n_slots, 4 row quarters, DPAD/4, 32, 4) fp32; all zero on entry, and again after the postprocess pass
+  // behind dsum (not a member: the kernels that do not use it keep their parameter block): int turn[h][n_slots][4 row quarters],
+  // FA_FLAG_DETERMINISTIC -- how many key blocks have added their part to that quarter tile; cleared by every call that uses it
   int n_slots;
 };
 __device__ __forceinline__ int tile_slot(int q_begin, int bidb, int m) { return (q_begin >> 7) + bidb + m; }
@@ -163,12 +165,20 @@ __device__ __forceinline__ void finalize_dq_quarter(float* acc, uint16_t* dq_row
 // ------------------------------------------------------------------------------------------------
 // main kernel
 // ------------------------------------------------------------------------------------------------
-// kTrim: head dim below DPAD -- issue only the MMA k-steps / output columns / dQ reduction chunks that hold data (a separate
-// instantiation: with the counts as run-time values the full-width kernels lose 3 % to the extra registers and branches)
-template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse, bool kAlibi, bool kTrim>
+// kMode 1 (trimmed): head dim below DPAD -- issue only the MMA k-steps / output columns / dQ reduction chunks that hold data (a
+// separate instantiation: with the counts as run-time values the full-width kernels lose 3 % to the extra registers and branches).
+// kMode 2 (deterministic, FA_FLAG_DETERMINISTIC): trimmed, and the key blocks add their dQ parts to a query tile one after the
+// other, in key-block order -- dQ becomes bitwise reproducible like dK and dV.  Per (head, tile, 32-row quarter) a counter in the
+// workspace holds how many key blocks have added their part; the drain warp of key block j waits for the value j, issues its
+// bulk reductions, waits until they have completed (written, not just read), and publishes j + 1.  Key block j only ever waits for
+// j - 1, whose CTA has a lower blockIdx in both launch orders, so it is running or done: no cycle.  A stalled turn traps after 4 s.
+template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse, bool kAlibi, int kMode>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, const BlockMaskView bm, const BwdWs ws,
                  const int n_kblocks, const int bh_group, const PhiloxKey pk) {   // round keys precomputed on the host (constant bank)
+  constexpr bool kTrim = kMode != 0;
+  constexpr bool kDet = kMode == 2;
+  static_assert(!(kDet && kSparse), "deterministic dQ: dense launches only (with a block mask the contributors of a tile are not 0..j)");
   using L = BwdSmem<DPAD>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -592,6 +602,25 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
         tc_fence_before();
         mbar_arrive(dq_empty);
       }
+      int* turn = nullptr;
+      if constexpr (kDet) {
+        // contributors of query tile m are the key blocks 0 .. min(m, last) (causal) or all of them, so this CTA's rank is n_blk
+        turn = reinterpret_cast<int*>(ws.dsum + (int64_t)p.h * ws.n_slots * kBM) + (((int64_t)bidh * ws.n_slots + slot0 + m) << 2) + wq;
+        if (lane == 0) {
+          uint64_t t0 = 0;
+          uint32_t spins = 0;
+          while (ld_acquire_gpu(turn) != n_blk) {
+            __nanosleep(64);
+            if ((++spins & 4095u) == 0) {
+              const uint64_t now = global_timer_ns();
+              if (t0 == 0) t0 = now;
+              else if (now - t0 > 4000000000ull) asm volatile("trap;\n");
+            }
+          }
+        }
+        fence_proxy_async_global();      // lane 0 issues the reductions: they are ordered behind its acquire
+        __syncwarp();
+      }
 #pragma unroll
       for (int k = 0; k < kChunks; ++k) {
         if (k < n_chunks) {
@@ -626,6 +655,15 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
             if (wq == 0) FA_TRACE(17);
           }
         }
+      }
+      if constexpr (kDet) {
+        if (lane == 0) {
+          bulk_wait_group<0>();          // this tile's reductions have been performed, not only read out of the staging buffers
+          fence_proxy_async_global();
+          __threadfence();
+          st_release_gpu(turn, n_blk + 1);
+        }
+        __syncwarp();
       }
       if (wq == 0) FA_TRACE(18);
     }
@@ -943,7 +981,7 @@ __global__ void __launch_bounds__(128) bwd_postprocess_kernel(const fa_params p,
 inline uint64_t align256(uint64_t x) { return (x + 255) & ~uint64_t(255); }
 
 struct BwdWsLayout {
-  uint64_t nl_off, dsum_off, accum_off, total;
+  uint64_t nl_off, dsum_off, accum_off, turn_off, total;
   int n_slots, dpad;
 };
 
@@ -955,7 +993,8 @@ BwdWsLayout bwd_ws_layout(const fa_params& p) {
   l.accum_off = 0;                                         // [0, nl_off): the "zero on entry / zero on exit" region
   l.nl_off = align256(rows * l.dpad * 4);
   l.dsum_off = l.nl_off + align256(rows * 4);
-  l.total = l.dsum_off + align256(rows * 4);
+  l.turn_off = l.dsum_off + rows * 4;                      // deterministic mode's turn counters, right behind dsum (rows * 4 is a multiple of 512)
+  l.total = l.turn_off + align256((uint64_t)p.h * l.n_slots * 4 * sizeof(int));
   return l;
 }
 
@@ -963,13 +1002,13 @@ BwdWsLayout bwd_ws_layout(const fa_params& p) {
 // kernel is bound by the dQ reduction traffic, which shrinks with the head dim; the dropout variants are ALU-bound and the
 // 64-column tile gains < 1 %).  The postprocess pass has to agree, hence one predicate for both.
 inline bool bwd_runs_trimmed(const fa_params& p, const BlockMaskView& bm) {
-  return p.d > 64 && ((p.d + 15) >> 4) < 8 && !(p.p_dropout > 0.f) && bm.dense == nullptr;
+  return p.d > 64 && ((p.d + 15) >> 4) < 8 && !(p.p_dropout > 0.f) && bm.dense == nullptr && !(p.flags & FA_FLAG_DETERMINISTIC);
 }
 
-template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse, bool kAlibi, bool kTrim = false>
+template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse, bool kAlibi, int kMode = 0>
 cudaError_t launch_bwd_variant(const BwdTensorMaps& maps, const fa_params& p, const BlockMaskView& bm, const BwdWs& ws,
                                cudaStream_t stream) {
-  auto kernel = bwd_sm100_kernel<DPAD, kBf16, kCausal, kDropout, kSparse, kAlibi, kTrim>;
+  auto kernel = bwd_sm100_kernel<DPAD, kBf16, kCausal, kDropout, kSparse, kAlibi, kMode>;
   constexpr int smem = BwdSmem<DPAD>::kDynamicBytes;
   static std::atomic<uint64_t> configured{0};   // bit per device (as in the forward)
   int dev = 0;
@@ -1000,13 +1039,27 @@ cudaError_t dispatch_bwd_flags(const BwdTensorMaps& maps, const fa_params& p, co
                 : launch_bwd_variant<DPAD, kBf16, false, false, true, false>(maps, p, bm, ws, stream);
   }
   const int sel = (p.is_causal ? 4 : 0) | (drop ? 2 : 0) | (p.alibi_slopes != nullptr ? 1 : 0);
+#ifndef FA_BWD_FEW_VARIANTS
+  if (p.flags & FA_FLAG_DETERMINISTIC) {
+    switch (sel) {
+      case 0: return launch_bwd_variant<DPAD, kBf16, false, false, false, false, 2>(maps, p, bm, ws, stream);
+      case 1: return launch_bwd_variant<DPAD, kBf16, false, false, false, true, 2>(maps, p, bm, ws, stream);
+      case 2: return launch_bwd_variant<DPAD, kBf16, false, true, false, false, 2>(maps, p, bm, ws, stream);
+      case 3: return launch_bwd_variant<DPAD, kBf16, false, true, false, true, 2>(maps, p, bm, ws, stream);
+      case 4: return launch_bwd_variant<DPAD, kBf16, true, false, false, false, 2>(maps, p, bm, ws, stream);
+      case 5: return launch_bwd_variant<DPAD, kBf16, true, false, false, true, 2>(maps, p, bm, ws, stream);
+      case 6: return launch_bwd_variant<DPAD, kBf16, true, true, false, false, 2>(maps, p, bm, ws, stream);
+      default: return launch_bwd_variant<DPAD, kBf16, true, true, false, true, 2>(maps, p, bm, ws, stream);
+    }
+  }
+#endif
   if constexpr (DPAD == 128) {
     if (bwd_runs_trimmed(p, bm)) {
       switch (sel) {
-        case 0: return launch_bwd_variant<DPAD, kBf16, false, false, false, false, true>(maps, p, bm, ws, stream);
-        case 1: return launch_bwd_variant<DPAD, kBf16, false, false, false, true, true>(maps, p, bm, ws, stream);
-        case 4: return launch_bwd_variant<DPAD, kBf16, true, false, false, false, true>(maps, p, bm, ws, stream);
-        default: return launch_bwd_variant<DPAD, kBf16, true, false, false, true, true>(maps, p, bm, ws, stream);
+        case 0: return launch_bwd_variant<DPAD, kBf16, false, false, false, false, 1>(maps, p, bm, ws, stream);
+        case 1: return launch_bwd_variant<DPAD, kBf16, false, false, false, true, 1>(maps, p, bm, ws, stream);
+        case 4: return launch_bwd_variant<DPAD, kBf16, true, false, false, false, 1>(maps, p, bm, ws, stream);
+        default: return launch_bwd_variant<DPAD, kBf16, true, false, false, true, 1>(maps, p, bm, ws, stream);
       }
     }
   }
@@ -1058,6 +1111,10 @@ cudaError_t launch_bwd_sm100(const fa_params& p, const BlockMaskView& bm, void* 
   cudaError_t e;
   if (!(p.flags & FA_FLAG_WS_ZEROED)) {
     e = cudaMemsetAsync(base + l.accum_off, 0, l.nl_off - l.accum_off, stream);
+    if (e != cudaSuccess) return e;
+  }
+  if (p.flags & FA_FLAG_DETERMINISTIC) {   // 16 bytes per (head, query tile): a memset node, so that no other kernel changes for it
+    e = cudaMemsetAsync(base + l.turn_off, 0, l.total - l.turn_off, stream);
     if (e != cudaSuccess) return e;
   }
   if (n_qtiles > 0 && p.total_q > 0) {

@@ -32,6 +32,8 @@ FA_DEVICE void mbar_init(uint64_t* bar, uint32_t count) {
 }
 FA_DEVICE void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory"); }
 FA_DEVICE void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
+// generic <-> async proxy ordering on global memory (the deterministic dQ turns: bulk reductions of two CTAs on the same lines)
+FA_DEVICE void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;\n" ::: "memory"); }
 
 FA_DEVICE void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(smem_u32(bar)) : "memory");
@@ -122,6 +124,12 @@ FA_DEVICE void red_add_v4_f32(float* gptr, uint32_t a, uint32_t b, uint32_t c, u
                :: "l"(gptr), "f"(__uint_as_float(a)), "f"(__uint_as_float(b)), "f"(__uint_as_float(c)), "f"(__uint_as_float(d))
                : "memory");
 }
+FA_DEVICE int ld_acquire_gpu(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.b32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+FA_DEVICE void st_release_gpu(int* p, int v) { asm volatile("st.release.gpu.global.b32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory"); }
 FA_DEVICE void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;\n" ::: "memory"); }
 template <int N>
 FA_DEVICE void bulk_wait_group_read() { asm volatile("cp.async.bulk.wait_group.read %0;\n" ::"n"(N) : "memory"); }

@@ -19,11 +19,30 @@ _LIB_PATH = os.environ.get("FA_B200_LIB") or os.path.join(_HERE, "csrc", "libfa_
 FA_IMPL_AUTO, FA_IMPL_TCGEN05, FA_IMPL_SIMT = 0, 1, 2
 FA_OP_FWD, FA_OP_BWD, FA_OP_FWD_BLOCK, FA_OP_BWD_BLOCK = 0, 1, 2, 3
 
-FA_FLAG_WS_ZEROED, FA_FLAG_KEEP_DQ_ACCUM = 1, 2
+FA_FLAG_WS_ZEROED, FA_FLAG_KEEP_DQ_ACCUM, FA_FLAG_DETERMINISTIC = 1, 2, 4
 
 # fa_params.impl of every call.  Always FA_IMPL_AUTO (the tcgen05 kernels) in the product; the GPU test-suite patches
 # this module attribute to FA_IMPL_SIMT to cross-check against the library's CUDA-core kernels (tests/fa_test_utils.py).
 _impl = FA_IMPL_AUTO
+
+# Bitwise reproducible dQ (FA_FLAG_DETERMINISTIC, include/fa_b200.h): None = follow torch.are_deterministic_algorithms_enabled().
+# dK, dV and the forward are reproducible in either mode; the blocksparse backward and the K/V ring's accumulating calls
+# (dq_workspace=) have no ordered mode and keep their fp32 reductions in arrival order.
+_deterministic = None
+
+
+def set_deterministic(mode):
+    """True / False: dQ of `bwd` is / is not accumulated in key-block order; None: follow torch's global switch
+    (torch.use_deterministic_algorithms).  Returns the previous setting."""
+    global _deterministic
+    if mode is not None and not isinstance(mode, bool):
+        raise TypeError("set_deterministic expects True, False or None")
+    prev, _deterministic = _deterministic, mode
+    return prev
+
+
+def _want_deterministic():
+    return torch.are_deterministic_algorithms_enabled() if _deterministic is None else _deterministic
 
 
 class FaParams(ctypes.Structure):
@@ -428,6 +447,8 @@ def _bwd_impl(dout, q, k, v, out, softmax_lse, dq, dk, dv, cu_seqlens_q, cu_seql
             P.dq = None
         else:
             ws = _workspace(P, op, q.device, stream)
+            if blockmask is None and P.impl != FA_IMPL_SIMT and _want_deterministic():
+                P.flags |= FA_FLAG_DETERMINISTIC
         _set_philox(P, _philox_state(p_dropout, gen, q.device, P, stream))
         fn = _lib.fa_bwd if blockmask is None else _lib.fa_bwd_block
         _raise_if_failed(fn(ctypes.byref(P), stream), "flash_attn_cuda.bwd")

@@ -1,4 +1,5 @@
-"""Kernel-level timing of one configuration: python tools/time_cfg.py b h d s causal p dtype(bf16|fp16) [reps]"""
+"""Kernel-level timing of one configuration: python tools/time_cfg.py b h d s causal p dtype(bf16|fp16) [reps] [det]
+(det: bitwise reproducible dQ, FA_FLAG_DETERMINISTIC)"""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -11,6 +12,8 @@ b, h, d, s = [int(x) for x in sys.argv[1:5]]
 causal, p = sys.argv[5] == "1", float(sys.argv[6])
 dtype = torch.bfloat16 if sys.argv[7] == "bf16" else torch.float16
 reps = int(sys.argv[8]) if len(sys.argv) > 8 else 10
+if len(sys.argv) > 9 and sys.argv[9] == "det":
+    flash_attn_cuda.set_deterministic(True)
 qkv = torch.randn(b * s, 3, h, d, device="cuda", dtype=dtype, requires_grad=True)
 dout = torch.randn(b * s, h, d, device="cuda", dtype=dtype)
 cu = torch.arange(0, (b + 1) * s, s, device="cuda", dtype=torch.int32)
