@@ -193,6 +193,67 @@ def test_invalid_arguments_are_rejected_without_a_gpu():
         flash_attn_cuda.fwd(q, q, q, cu, cu, 4, 4, 0.0, 1.0, False, False, False, None)
 
 
+def _bwd_params(b=16, h=12, d=128, s=4096):
+    import flash_attn_cuda as F
+    P = F.FaParams()
+    P.b, P.h, P.d, P.total_q, P.total_k = b, h, d, b * s, b * s
+    P.max_seqlen_q = P.max_seqlen_k = P.seqlen_q_rounded = P.seqlen_k_rounded = s
+    for f in ("q", "k", "v", "o", "dout", "dq", "dk", "dv", "softmax_lse", "softmax_d", "cu_seqlens_q", "cu_seqlens_k"):
+        setattr(P, f, 0x10000)        # never dereferenced: argument validation happens on the host
+    for f in ("q", "k", "v", "o", "do", "dq", "dk", "dv"):
+        setattr(P, f + "_row_stride", h * d)
+        setattr(P, f + "_head_stride", d)
+    P.softmax_scale = 1.0
+    return P
+
+
+@pytest.mark.parametrize("d,dpad", [(128, 128), (96, 128), (64, 64), (40, 64)])
+def test_backward_workspace_layout_is_linear_in_total_q(d, dpad):
+    """fp32 dQ accumulator (the range that is zero on entry and on exit, at byte 0), two fp32 statistics per row, 16
+    bytes of turn counters per (head, tile slot); slots = total_q / 128 + batch + 1, independent of max_seqlen."""
+    import flash_attn_cuda as F
+    b, h, s = 16, 12, 4096
+    P = _bwd_params(b, h, d, s)
+    slots = (b * s >> 7) + b + 1
+    accum, stats, turn = h * slots * 128 * dpad * 4, h * slots * 128 * 4, (h * slots * 16 + 255) // 256 * 256
+    assert F._lib.fa_workspace_bytes(ctypes.byref(P), F.FA_OP_BWD) == accum + 2 * stats + turn
+    off = ctypes.c_uint64(99)
+    assert F._lib.fa_workspace_zero_range(ctypes.byref(P), F.FA_OP_BWD, ctypes.byref(off)) == accum and off.value == 0
+    P.max_seqlen_q = P.seqlen_q_rounded = 8 * s          # one long sequence among short ones does not grow it
+    assert F._lib.fa_workspace_bytes(ctypes.byref(P), F.FA_OP_BWD) == accum + 2 * stats + turn
+
+
+def test_flag_combinations_are_validated_on_the_host():
+    import flash_attn_cuda as F
+    P = _bwd_params()
+    P.workspace, P.workspace_bytes = 0x10000, F._lib.fa_workspace_bytes(ctypes.byref(P), F.FA_OP_BWD)
+    P.flags = F.FA_FLAG_DETERMINISTIC | F.FA_FLAG_KEEP_DQ_ACCUM | F.FA_FLAG_WS_ZEROED
+    assert F._lib.fa_bwd(ctypes.byref(P), None) == 1 and b"FA_FLAG_DETERMINISTIC applies to fa_bwd" in F._lib.fa_last_error()
+    P.flags = F.FA_FLAG_DETERMINISTIC
+    assert F._lib.fa_fwd(ctypes.byref(P), None) == 1 and b"FA_FLAG_DETERMINISTIC" in F._lib.fa_last_error()
+    P.flags = F.FA_FLAG_KEEP_DQ_ACCUM
+    assert F._lib.fa_bwd(ctypes.byref(P), None) == 1 and b"needs FA_FLAG_WS_ZEROED" in F._lib.fa_last_error()
+    P.flags = 8
+    assert F._lib.fa_bwd(ctypes.byref(P), None) == 1 and b"unknown flags" in F._lib.fa_last_error()
+
+
+def test_deterministic_switch_follows_torch_unless_set():
+    import flash_attn_cuda as F
+    assert F._deterministic is None and F._want_deterministic() == torch.are_deterministic_algorithms_enabled()
+    try:
+        assert F.set_deterministic(True) is None and F._want_deterministic()
+        assert F.set_deterministic(False) is True and not F._want_deterministic()
+        torch.use_deterministic_algorithms(True, warn_only=True)
+        assert not F._want_deterministic()                      # an explicit setting wins over torch's switch
+        assert F.set_deterministic(None) is False and F._want_deterministic()
+        with pytest.raises(TypeError):
+            F.set_deterministic(1)
+    finally:
+        torch.use_deterministic_algorithms(False)
+        F.set_deterministic(None)
+    assert not F._want_deterministic()
+
+
 def test_dropout_stream_statistics_host():
     """The position-keyed Philox stream (integer work, evaluated on the host) keeps ~(1-p) of positions."""
     import flash_attn_cuda
