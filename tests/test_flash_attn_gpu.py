@@ -158,11 +158,14 @@ def test_flash_attn_unpadded(seqlen, d, dropout_p, causal, dtype):
 @pytest.mark.parametrize("d", [128, 64, 32, 16])
 @pytest.mark.parametrize("seqlen", SEQLENS)
 @pytest.mark.parametrize("dropout_p", [0.0, 0.17])
-def test_flash_attn_race_condition(seqlen, d, dropout_p, causal, dtype):
+@pytest.mark.parametrize("ordered_dq", [False, True])
+def test_flash_attn_race_condition(seqlen, d, dropout_p, causal, dtype, ordered_dq):
     """tests/test_flash_attn.py:610-671: bitwise run-to-run determinism of O and S_dmask (the reference's asserts)
     and, here, of dK and dV.  dQ is accumulated across key blocks with fp32 bulk reductions in global memory
-    (north_star: "dQ is accumulated by atomics"), so its summation order may differ run to run: it must agree to
-    fp32 round-off, far below the 16-bit output resolution."""
+    (north_star: "dQ is accumulated by atomics"), so by default its summation order may differ run to run: it must
+    agree to fp32 round-off, far below the 16-bit output resolution.  ordered_dq: with FA_FLAG_DETERMINISTIC
+    (flash_attn_cuda.set_deterministic) the key blocks take turns and dQ is bitwise reproducible too, 10 runs."""
+    import flash_attn_cuda
     fi = _api()
     q, k, v = make_inputs(seqlen, d, dtype)
     qmask = orc.generate_random_padding_mask(seqlen, BATCH, "cuda", mode="random")
@@ -178,14 +181,19 @@ def test_flash_attn_race_condition(seqlen, d, dropout_p, causal, dtype):
         grads = torch.autograd.grad(out, (P.q_unpad, P.k_unpad, P.v_unpad), g)
         return (out, S) + tuple(grads)
 
-    first = run()
-    for _ in range(10):
-        again = run()
-        for i, (a, b) in enumerate(zip(first, again)):
-            if i == 2:   # dQ
-                assert torch.allclose(a.float(), b.float(), rtol=2e-2, atol=1e-3 * max(1.0, a.abs().max().item()))
-            else:
-                assert torch.equal(a, b)
+    prev = flash_attn_cuda.set_deterministic(True) if ordered_dq else None
+    try:
+        first = run()
+        for _ in range(10):
+            again = run()
+            for i, (a, b) in enumerate(zip(first, again)):
+                if i == 2 and not ordered_dq:   # dQ
+                    assert torch.allclose(a.float(), b.float(), rtol=2e-2, atol=1e-3 * max(1.0, a.abs().max().item()))
+                else:
+                    assert torch.equal(a, b)
+    finally:
+        if ordered_dq:
+            flash_attn_cuda.set_deterministic(prev)
 
 
 @pytest.mark.parametrize("dtype", DTYPES)
