@@ -623,27 +623,27 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
       }
 #pragma unroll
       for (int k = 0; k < kChunks; ++k) {
-        if (k < n_chunks) {
-        const uint32_t buf = n_issued % L::kDqBufs;
-        if (n_issued >= L::kDqBufs) {
-          if (lane == 0) bulk_wait_group_read<L::kDqBufs - 1>();   // the bulk op that last read this buffer is done with it
-          __syncwarp();
-        }
-        ++n_issued;
-        const uint32_t dst = stage + buf * 2048 + lane * 16;
+        if (k < n_chunks) {   // kTrim: chunks past the head dim are neither staged nor reduced
+          const uint32_t buf = n_issued % L::kDqBufs;
+          if (n_issued >= L::kDqBufs) {
+            if (lane == 0) bulk_wait_group_read<L::kDqBufs - 1>();   // the bulk op that last read this buffer is done with it
+            __syncwarp();
+          }
+          ++n_issued;
+          const uint32_t dst = stage + buf * 2048 + lane * 16;
 #ifndef FA_BWD_EXP_NO_DRAIN
 #pragma unroll
-        for (int g = 0; g < 4; ++g)
-          st_shared_v4(dst + g * 512, v[k % kRing][4 * g], v[k % kRing][4 * g + 1], v[k % kRing][4 * g + 2], v[k % kRing][4 * g + 3]);
-        fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) {
-          bulk_reduce_add_f32(gdst + k * 512, stage_gen + buf * 2048, 2048);
-          bulk_commit_group();
-        }
+          for (int g = 0; g < 4; ++g)
+            st_shared_v4(dst + g * 512, v[k % kRing][4 * g], v[k % kRing][4 * g + 1], v[k % kRing][4 * g + 2], v[k % kRing][4 * g + 3]);
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            bulk_reduce_add_f32(gdst + k * 512, stage_gen + buf * 2048, 2048);
+            bulk_commit_group();
+          }
 #else
-        if (v[k % kRing][0] == 0x7fc12345u) st_shared_v4(dst, 0, 0, 0, 0);   // timing experiment: no staging, no reduction
-        if (lane == 0) bulk_commit_group();
+          if (v[k % kRing][0] == 0x7fc12345u) st_shared_v4(dst, 0, 0, 0, 0);   // timing experiment: no staging, no reduction
+          if (lane == 0) bulk_commit_group();
 #endif
         }
         if (k + kRing < kChunks) {
