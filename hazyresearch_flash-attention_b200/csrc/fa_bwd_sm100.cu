@@ -30,6 +30,16 @@
 #include "fa_kernels.h"
 #include "sm100_ptx.cuh"
 
+// This file is compiled three times (Makefile), each time with another share of the 88 instantiations of the main kernel, so
+// that the build is three parallel jobs instead of one two-minute one:
+//   FA_BWD_PART 0  host side, preprocess / postprocess kernels, the 128-column main kernels (plain and trimmed)
+//   FA_BWD_PART 1  the 64-column main kernels                       -> bwd_dispatch_d64()
+//   FA_BWD_PART 2  the ordered-dQ (FA_FLAG_DETERMINISTIC) kernels   -> bwd_dispatch_ordered()
+// (-DFA_BWD_FEW_VARIANTS experiment builds are a single part-0 object with two or three instantiations.)
+#ifndef FA_BWD_PART
+#define FA_BWD_PART 0
+#endif
+
 namespace fa {
 
 namespace {
@@ -73,6 +83,9 @@ struct BwdSmem {
 };
 static_assert(BwdSmem<128>::kDynamicBytes <= 232448, "shared memory budget");
 
+}  // namespace
+
+// (named namespace: these two appear in the signatures that cross the three objects)
 struct BwdTensorMaps {
   CUtensorMap q, k, v, dout;
 };
@@ -88,6 +101,11 @@ struct BwdWs {
   // FA_FLAG_DETERMINISTIC -- how many key blocks have added their part to that quarter tile; cleared by every call that uses it
   int n_slots;
 };
+cudaError_t bwd_dispatch_d64(const BwdTensorMaps& maps, const fa_params& p, const BlockMaskView& bm, const BwdWs& ws, cudaStream_t stream);
+cudaError_t bwd_dispatch_ordered(const BwdTensorMaps& maps, const fa_params& p, const BlockMaskView& bm, const BwdWs& ws, cudaStream_t stream);
+
+namespace {
+
 __device__ __forceinline__ int tile_slot(int q_begin, int bidb, int m) { return (q_begin >> 7) + bidb + m; }
 
 // Optional timeline tracing of one CTA (build with -DFA_BWD_TRACE; tools/trace_bwd.py): clock64 at pipeline events.
@@ -898,6 +916,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
 #endif
 }
 
+#if FA_BWD_PART == 0
 // ------------------------------------------------------------------------------------------------
 // preprocess: D = rowsum(dO o O) -> softmax_d and the workspace copy; -lse*log2e -> workspace (both padded to whole
 // 128-row tiles of each sequence).  HBM-bound: 16 threads per query row (16 bytes each), 64 rows per CTA, all eight
@@ -1004,6 +1023,7 @@ BwdWsLayout bwd_ws_layout(const fa_params& p) {
 inline bool bwd_runs_trimmed(const fa_params& p, const BlockMaskView& bm) {
   return p.d > 64 && ((p.d + 15) >> 4) < 8 && !(p.p_dropout > 0.f) && bm.dense == nullptr && !(p.flags & FA_FLAG_DETERMINISTIC);
 }
+#endif   // FA_BWD_PART == 0
 
 template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse, bool kAlibi, int kMode = 0>
 cudaError_t launch_bwd_variant(const BwdTensorMaps& maps, const fa_params& p, const BlockMaskView& bm, const BwdWs& ws,
@@ -1030,52 +1050,51 @@ cudaError_t launch_bwd_variant(const BwdTensorMaps& maps, const fa_params& p, co
   return cudaGetLastError();
 }
 
-template <int DPAD, bool kBf16>
-cudaError_t dispatch_bwd_flags(const BwdTensorMaps& maps, const fa_params& p, const BlockMaskView& bm, const BwdWs& ws,
+// dense launches: causal x dropout x alibi for one tile width, dtype and kernel mode (the trimmed mode has no dropout variants)
+template <int DPAD, bool kBf16, int kMode>
+cudaError_t dispatch_bwd_dense(const BwdTensorMaps& maps, const fa_params& p, const BlockMaskView& bm, const BwdWs& ws,
                                cudaStream_t stream) {
-  const bool drop = p.p_dropout > 0.f;
-  if (bm.dense != nullptr) {
-    return drop ? launch_bwd_variant<DPAD, kBf16, false, true, true, false>(maps, p, bm, ws, stream)
-                : launch_bwd_variant<DPAD, kBf16, false, false, true, false>(maps, p, bm, ws, stream);
-  }
-  const int sel = (p.is_causal ? 4 : 0) | (drop ? 2 : 0) | (p.alibi_slopes != nullptr ? 1 : 0);
-#ifndef FA_BWD_FEW_VARIANTS
-  if (p.flags & FA_FLAG_DETERMINISTIC) {
+  const int sel = (p.is_causal ? 4 : 0) | (p.p_dropout > 0.f ? 2 : 0) | (p.alibi_slopes != nullptr ? 1 : 0);
+  if constexpr (kMode != 1) {
     switch (sel) {
-      case 0: return launch_bwd_variant<DPAD, kBf16, false, false, false, false, 2>(maps, p, bm, ws, stream);
-      case 1: return launch_bwd_variant<DPAD, kBf16, false, false, false, true, 2>(maps, p, bm, ws, stream);
-      case 2: return launch_bwd_variant<DPAD, kBf16, false, true, false, false, 2>(maps, p, bm, ws, stream);
-      case 3: return launch_bwd_variant<DPAD, kBf16, false, true, false, true, 2>(maps, p, bm, ws, stream);
-      case 4: return launch_bwd_variant<DPAD, kBf16, true, false, false, false, 2>(maps, p, bm, ws, stream);
-      case 5: return launch_bwd_variant<DPAD, kBf16, true, false, false, true, 2>(maps, p, bm, ws, stream);
-      case 6: return launch_bwd_variant<DPAD, kBf16, true, true, false, false, 2>(maps, p, bm, ws, stream);
-      default: return launch_bwd_variant<DPAD, kBf16, true, true, false, true, 2>(maps, p, bm, ws, stream);
+      case 2: return launch_bwd_variant<DPAD, kBf16, false, true, false, false, kMode>(maps, p, bm, ws, stream);
+      case 3: return launch_bwd_variant<DPAD, kBf16, false, true, false, true, kMode>(maps, p, bm, ws, stream);
+      case 6: return launch_bwd_variant<DPAD, kBf16, true, true, false, false, kMode>(maps, p, bm, ws, stream);
+      case 7: return launch_bwd_variant<DPAD, kBf16, true, true, false, true, kMode>(maps, p, bm, ws, stream);
+      default: break;
     }
   }
-#endif
-  if constexpr (DPAD == 128) {
-    if (bwd_runs_trimmed(p, bm)) {
-      switch (sel) {
-        case 0: return launch_bwd_variant<DPAD, kBf16, false, false, false, false, 1>(maps, p, bm, ws, stream);
-        case 1: return launch_bwd_variant<DPAD, kBf16, false, false, false, true, 1>(maps, p, bm, ws, stream);
-        case 4: return launch_bwd_variant<DPAD, kBf16, true, false, false, false, 1>(maps, p, bm, ws, stream);
-        default: return launch_bwd_variant<DPAD, kBf16, true, false, false, true, 1>(maps, p, bm, ws, stream);
-      }
-    }
-  }
-  switch (sel) {
-    case 0: return launch_bwd_variant<DPAD, kBf16, false, false, false, false>(maps, p, bm, ws, stream);
-    case 1: return launch_bwd_variant<DPAD, kBf16, false, false, false, true>(maps, p, bm, ws, stream);
-    case 2: return launch_bwd_variant<DPAD, kBf16, false, true, false, false>(maps, p, bm, ws, stream);
-    case 3: return launch_bwd_variant<DPAD, kBf16, false, true, false, true>(maps, p, bm, ws, stream);
-    case 4: return launch_bwd_variant<DPAD, kBf16, true, false, false, false>(maps, p, bm, ws, stream);
-    case 5: return launch_bwd_variant<DPAD, kBf16, true, false, false, true>(maps, p, bm, ws, stream);
-    case 6: return launch_bwd_variant<DPAD, kBf16, true, true, false, false>(maps, p, bm, ws, stream);
-    default: return launch_bwd_variant<DPAD, kBf16, true, true, false, true>(maps, p, bm, ws, stream);
+  switch (sel & 5) {
+    case 0: return launch_bwd_variant<DPAD, kBf16, false, false, false, false, kMode>(maps, p, bm, ws, stream);
+    case 1: return launch_bwd_variant<DPAD, kBf16, false, false, false, true, kMode>(maps, p, bm, ws, stream);
+    case 4: return launch_bwd_variant<DPAD, kBf16, true, false, false, false, kMode>(maps, p, bm, ws, stream);
+    default: return launch_bwd_variant<DPAD, kBf16, true, false, false, true, kMode>(maps, p, bm, ws, stream);
   }
 }
 
+// block mask: non-causal, no bias (flash_blocksparse_attn_interface.py:21)
+template <int DPAD, bool kBf16>
+cudaError_t dispatch_bwd_sparse(const BwdTensorMaps& maps, const fa_params& p, const BlockMaskView& bm, const BwdWs& ws,
+                                cudaStream_t stream) {
+  return p.p_dropout > 0.f ? launch_bwd_variant<DPAD, kBf16, false, true, true, false>(maps, p, bm, ws, stream)
+                           : launch_bwd_variant<DPAD, kBf16, false, false, true, false>(maps, p, bm, ws, stream);
+}
+
 }  // namespace
+
+#if FA_BWD_PART == 1
+cudaError_t bwd_dispatch_d64(const BwdTensorMaps& maps, const fa_params& p, const BlockMaskView& bm, const BwdWs& ws, cudaStream_t stream) {
+  if (bm.dense != nullptr)
+    return p.is_bf16 ? dispatch_bwd_sparse<64, true>(maps, p, bm, ws, stream) : dispatch_bwd_sparse<64, false>(maps, p, bm, ws, stream);
+  return p.is_bf16 ? dispatch_bwd_dense<64, true, 0>(maps, p, bm, ws, stream) : dispatch_bwd_dense<64, false, 0>(maps, p, bm, ws, stream);
+}
+#elif FA_BWD_PART == 2
+cudaError_t bwd_dispatch_ordered(const BwdTensorMaps& maps, const fa_params& p, const BlockMaskView& bm, const BwdWs& ws, cudaStream_t stream) {
+  if (p.d <= 64)
+    return p.is_bf16 ? dispatch_bwd_dense<64, true, 2>(maps, p, bm, ws, stream) : dispatch_bwd_dense<64, false, 2>(maps, p, bm, ws, stream);
+  return p.is_bf16 ? dispatch_bwd_dense<128, true, 2>(maps, p, bm, ws, stream) : dispatch_bwd_dense<128, false, 2>(maps, p, bm, ws, stream);
+}
+#else
 
 uint64_t bwd_sm100_workspace_bytes(const fa_params& p) { return bwd_ws_layout(p).total; }
 uint64_t bwd_sm100_workspace_zero_bytes(const fa_params& p) { return bwd_ws_layout(p).nl_off; }
@@ -1149,8 +1168,11 @@ cudaError_t launch_bwd_sm100(const fa_params& p, const BlockMaskView& bm, void* 
                             : launch_bwd_variant<64, false, true, false, false, false>(maps, p, bm, ws, stream);
     else e = cudaErrorNotSupported;
 #else
-    if (p.d <= 64) e = p.is_bf16 ? dispatch_bwd_flags<64, true>(maps, p, bm, ws, stream) : dispatch_bwd_flags<64, false>(maps, p, bm, ws, stream);
-    else e = p.is_bf16 ? dispatch_bwd_flags<128, true>(maps, p, bm, ws, stream) : dispatch_bwd_flags<128, false>(maps, p, bm, ws, stream);
+    if (p.flags & FA_FLAG_DETERMINISTIC) e = bwd_dispatch_ordered(maps, p, bm, ws, stream);      // dense only (fa_api.cu validates)
+    else if (p.d <= 64) e = bwd_dispatch_d64(maps, p, bm, ws, stream);
+    else if (bm.dense != nullptr) e = p.is_bf16 ? dispatch_bwd_sparse<128, true>(maps, p, bm, ws, stream) : dispatch_bwd_sparse<128, false>(maps, p, bm, ws, stream);
+    else if (bwd_runs_trimmed(p, bm)) e = p.is_bf16 ? dispatch_bwd_dense<128, true, 1>(maps, p, bm, ws, stream) : dispatch_bwd_dense<128, false, 1>(maps, p, bm, ws, stream);
+    else e = p.is_bf16 ? dispatch_bwd_dense<128, true, 0>(maps, p, bm, ws, stream) : dispatch_bwd_dense<128, false, 0>(maps, p, bm, ws, stream);
 #endif
     if (e != cudaSuccess) return e;
   }
@@ -1196,5 +1218,7 @@ cudaError_t launch_bwd_dq_finalize(const fa_params& p, void* workspace, cudaStre
   count_launch();
   return cudaGetLastError();
 }
+
+#endif   // FA_BWD_PART
 
 }  // namespace fa
