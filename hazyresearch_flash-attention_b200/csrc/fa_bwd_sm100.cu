@@ -187,9 +187,10 @@ __device__ __forceinline__ void finalize_dq_quarter(float* acc, uint16_t* dq_row
 // separate instantiation: with the counts as run-time values the full-width kernels lose 3 % to the extra registers and branches).
 // kMode 2 (deterministic, FA_FLAG_DETERMINISTIC): trimmed, and the key blocks add their dQ parts to a query tile one after the
 // other, in key-block order -- dQ becomes bitwise reproducible like dK and dV.  Per (head, tile, 32-row quarter) a counter in the
-// workspace holds how many key blocks have added their part; the drain warp of key block j waits for the value j, issues its
-// bulk reductions, waits until they have completed (written, not just read), and publishes j + 1.  Key block j only ever waits for
-// j - 1, whose CTA has a lower blockIdx in both launch orders, so it is running or done: no cycle.  A stalled turn traps after 4 s.
+// workspace holds how many key blocks have added their part; the drain warp of a key block waits for the value that equals its
+// rank on that tile, issues its bulk reductions, waits until they have completed (written, not just read), and publishes
+// rank + 1.  The ranks follow the order in which the blocks reach a tile anyway (see tile_of below), and a block only ever waits
+// for CTAs that are running or done.  A stalled turn traps after 4 s.
 template <int DPAD, bool kBf16, bool kCausal, bool kDropout, bool kSparse, bool kAlibi, int kMode>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, const BlockMaskView bm, const BwdWs ws,
@@ -207,7 +208,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
   int bidb, bidh, n_blk;
   if (kCausal) {
     const CtaCoord c = decode_cta(blockIdx.x, n_kblocks, p.b * p.h, bh_group);
-    n_blk = c.x;
+    n_blk = kDet ? n_kblocks - 1 - c.x : c.x;   // ordered dQ: SHORTEST first (see the drain warps), so a CTA only waits for earlier ones
     bidb = c.bh / p.h;
     bidh = c.bh - bidb * p.h;
   } else {
@@ -621,13 +622,19 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
         mbar_arrive(dq_empty);
       }
       int* turn = nullptr;
+      int det_rank = 0;
       if constexpr (kDet) {
-        // contributors of query tile m are the key blocks 0 .. min(m, last) (causal) or all of them, so this CTA's rank is n_blk
+        // This CTA's rank among the key blocks that add to query tile m.  The turn order should be the order in which the blocks
+        // reach the tile anyway, or they end up a hand-over latency apart each.  Causal: block j starts on the diagonal tile
+        // m = j and walks down, so tile m sees blocks min(m, last), ..., 1, 0 one tile time apart: rank counts down from the
+        // diagonal, and the launch order is SHORTEST block first (decode above), so that block j waits for j + 1, which has
+        // a lower blockIdx.  Non-causal: every block walks the tiles in order, rank = j, block j waits for j - 1.
+        det_rank = kCausal ? min(m, (seq.seqlen_k + kBN - 1) / kBN - 1) - n_blk : n_blk;
         turn = reinterpret_cast<int*>(ws.dsum + (int64_t)p.h * ws.n_slots * kBM) + (((int64_t)bidh * ws.n_slots + slot0 + m) << 2) + wq;
         if (lane == 0) {
           uint64_t t0 = 0;
           uint32_t spins = 0;
-          while (ld_acquire_gpu(turn) != n_blk) {
+          while (ld_acquire_gpu(turn) != det_rank) {
             __nanosleep(64);
             if ((++spins & 4095u) == 0) {
               const uint64_t now = global_timer_ns();
@@ -679,7 +686,7 @@ bwd_sm100_kernel(const __grid_constant__ BwdTensorMaps maps, const fa_params p, 
           bulk_wait_group<0>();          // this tile's reductions have been performed, not only read out of the staging buffers
           fence_proxy_async_global();
           __threadfence();
-          st_release_gpu(turn, n_blk + 1);
+          st_release_gpu(turn, det_rank + 1);
         }
         __syncwarp();
       }

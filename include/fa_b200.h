@@ -124,8 +124,9 @@ enum {
   FA_FLAG_KEEP_DQ_ACCUM = 2u,
   /* backward (fa_bwd, tcgen05 kernels, no block mask): bitwise reproducible dQ.  By default the key blocks of a sequence add
    * their dQ parts to a query tile with fp32 reductions in whatever order they get there, so dQ varies in the last bits from
-   * run to run (dK and dV never do); with this flag they take turns in key-block order.  The main backward kernel then takes
-   * 1.3x (d = 64 with dropout) to 2.6x (d = 128 non-causal) as long: every hand-over waits for the reductions to complete.
+   * run to run (dK and dV never do); with this flag they take turns in a fixed order.  The main backward kernel then takes
+   * 1.2x (d = 64 causal with dropout) to 1.7x (d = 128 causal) and 2.6x (d = 128 non-causal) as long: every hand-over waits
+   * for the reductions to complete.
    * Not combinable with FA_FLAG_KEEP_DQ_ACCUM.  No counterpart in the reference's interface: its kernels walk the key blocks
    * of a (batch, head) pair inside one CTA (forward: fmha_fprop_kernel_1xN.h:686-717; the backward sources are not in the
    * snapshot), an ordered accumulation by construction; this flag is how to get an ordered dQ from this library. */
