@@ -1,7 +1,7 @@
 """Rotary position embeddings used by FlashMHA(use_rotary_emb=...).  Behavioural equivalent of the reference's
 pure-PyTorch flash_attn/rotary.py (interleaved pairs (x0, x1), (x2, x3), ...; tables cached per sequence length).
 The modules keep the reference's elementwise formulation (any device); FlashMHA goes through `apply_rotary_qkvpacked_`,
-which rotates q and k of the packed qkv tensor in place with one CUDA kernel (fa_rotary_qk) instead of the reference's
+which rotates q and k of the packed qkv tensor (and copies v) in one CUDA kernel pass (fa_rotary_qk) instead of the reference's
 elementwise passes + torch.stack copy (flash_attention.py:105-110)."""
 import math
 from typing import Tuple
