@@ -281,3 +281,32 @@ def test_package_resolves_into_repo():
     from flash_attn.flash_attention import FlashAttention, FlashMHA   # noqa: F401
     from flash_attn.flash_blocksparse_attn_interface import flash_blocksparse_attn_func   # noqa: F401
     from flash_attn.flash_blocksparse_attention import FlashBlocksparseAttention, FlashBlocksparseMHA   # noqa: F401
+
+
+def test_product_never_touches_the_oracle_or_a_fallback():
+    """The oracle is test infrastructure: nothing under the package may import it, and the package holds no second backend
+    (no Triton / torch.compile / SDPA call that could stand in for the CUDA library)."""
+    import ast
+    pkg = os.path.join(ROOT, "hazyresearch_flash-attention_b200")
+    n_files = 0
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if not f.endswith(".py"):
+                continue
+            n_files += 1
+            path = os.path.join(dirpath, f)
+            tree = ast.parse(open(path).read())
+            for node in ast.walk(tree):
+                names = []
+                if isinstance(node, ast.Import):
+                    names = [a.name for a in node.names]
+                elif isinstance(node, ast.ImportFrom):
+                    names = [node.module or ""]
+                for n in names:
+                    assert n.split(".")[0] not in ("oracle", "triton", "tilelang", "flashinfer", "vllm", "cutlass"), (path, n)
+                if isinstance(node, ast.Attribute):
+                    assert node.attr not in ("scaled_dot_product_attention", "compile"), (path, node.attr)
+    assert n_files >= 8
+    # an upstream flash_attn wheel is installed in this image: the package must shadow it, not use it
+    import flash_attn_cuda
+    assert not hasattr(flash_attn_cuda, "flash_attn_2_cuda")
