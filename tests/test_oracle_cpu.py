@@ -310,3 +310,37 @@ def test_product_never_touches_the_oracle_or_a_fallback():
     # an upstream flash_attn wheel is installed in this image: the package must shadow it, not use it
     import flash_attn_cuda
     assert not hasattr(flash_attn_cuda, "flash_attn_2_cuda")
+
+
+def test_header_is_plain_c_and_links_from_c(tmp_path):
+    """The drop-in boundary is a C ABI: include/fa_b200.h has to compile as C99 (cgo / ctypes / JNI bindings read it as C), and a C
+    program has to link against the library and get sane answers from the host-side entry points."""
+    import shutil
+    import subprocess
+    if shutil.which("gcc") is None:
+        pytest.skip("gcc not on PATH")
+    hdr = os.path.join(ROOT, "include", "fa_b200.h")
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", "-x", "c", hdr], check=True)
+    src = tmp_path / "probe.c"
+    src.write_text(r"""
+#include <stdio.h>
+#include <string.h>
+#include "fa_b200.h"
+int main(void) {
+  fa_params p;
+  memset(&p, 0, sizeof p);
+  if (fa_sizeof_params() != sizeof p) return 2;
+  if (fa_fwd(&p, 0) == FA_OK) return 3;                       /* an empty block is rejected on the host ... */
+  if (strstr(fa_last_error(), "batch size") == 0) return 4;   /* ... with a message */
+  p.p_dropout = 0.1f;
+  if (fa_philox_increment(&p) <= 0) return 5;
+  printf("abi %d\n", fa_abi_version());
+  return 0;
+}
+""")
+    exe = tmp_path / "probe"
+    libdir = os.path.dirname(LIB)
+    subprocess.run(["gcc", "-std=c99", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe), "-L", libdir, "-lfa_b200",
+                    f"-Wl,-rpath,{libdir}"], check=True)
+    out = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert out.returncode == 0 and out.stdout.strip() == "abi 2", (out.returncode, out.stdout, out.stderr)
