@@ -36,3 +36,19 @@ def test_product_arm_has_no_cpu_fallback():
     r = _run("--steps", "1", "--warmup", "1", "--no-cpu-baseline")
     assert r.returncode != 0
     assert not any(l.startswith("{") for l in r.stdout.splitlines())    # no number without the GPU path
+
+
+def test_reference_arm_under_torchrun_prints_one_line_from_rank_0():
+    """launched like the driver launches N > 1: rank 0 alone measures and prints, the other rank exits 0 without work"""
+    import socket
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", str(port), os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1",
+                        "--warmup", "1"], capture_output=True, text=True, cwd=ROOT, timeout=900)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [l for l in r.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["n_gpus"] == 2 and d["cpu_baseline"]["kind"] == "port"
